@@ -1,0 +1,114 @@
+/* b200slam — C ABI of the B200-native dense-SLAM backend hot path.
+ *
+ * Drop-in boundary for the reference's `mast3r_slam_backends` extension
+ * (Looong01/Splatt3R-SLAM, splatt3r_slam/backend).  Every entry point takes plain device
+ * pointers + extents + a CUDA stream (passed as void*, i.e. a cudaStream_t) and returns 0 on
+ * success or a negative B200SLAM_E* / positive cudaError_t code.  No torch types.  All tensors
+ * are row-major contiguous, exactly the layouts the reference's pybind functions receive
+ * (include/gn.h:22-117, src/gn.cpp:116-123).
+ *
+ * The library is compiled for sm_100a only; there is no CPU fallback.
+ */
+#ifndef B200SLAM_H
+#define B200SLAM_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200SLAM_OK 0
+#define B200SLAM_EINVAL (-1)    /* bad argument (null pointer, negative extent, n not supported) */
+#define B200SLAM_EWORKSPACE (-2) /* workspace too small */
+
+/* Residual model of the Gauss-Newton build. */
+#define B200SLAM_GN_RAYS 0   /* ray + distance, gn_kernels.cu:812-1137 (ray_align_kernel)   */
+#define B200SLAM_GN_CALIB 1  /* pixel + log-depth, gn_kernels.cu:1230-1542 (calib_proj_kernel) */
+#define B200SLAM_GN_POINTS 2 /* 3-D point, gn_kernels.cu:454-722 (point_align_kernel)        */
+
+int b200slam_version(void);
+
+/* Replaces iter_proj_cuda / iter_proj_kernel, matching_kernels.cu:118-315 (pybind gn.cpp:84-99).
+ * rays_img (b,h,w,9) f32; pts_3d_norm (b,n,3) f32; p_init (b,n,2) f32 (u,v)
+ * -> p_new (b,n,2) f32; converged (b,n) u8 (torch.bool storage).  Bit-exact with the reference. */
+int b200slam_iter_proj(const float *rays_img, const float *pts_3d_norm, const float *p_init,
+                       float *p_new, uint8_t *converged, int b, int h, int w, int n, int max_iter,
+                       float lambda_init, float cost_thresh, void *stream);
+
+/* Replaces refine_matches_cuda / refine_matches_kernel<c10::Half>, matching_kernels.cu:24-115
+ * (pybind gn.cpp:101-114).  D11 (b,h,w,fdim) f16; D21 (b,n,fdim) f16; p1 (b,n,2) i64 (u,v)
+ * -> p1_new (b,n,2) i64.  Bit-exact with the reference (sequential fp16-rounded MACs). */
+int b200slam_refine_matches_f16(const void *D11, const void *D21, const int64_t *p1,
+                                int64_t *p1_new, int b, int h, int w, int n, int fdim, int radius,
+                                int dilation_max, void *stream);
+/* float instantiation of the same kernel (AT_DISPATCH at matching_kernels.cu:102). */
+int b200slam_refine_matches_f32(const float *D11, const float *D21, const int64_t *p1,
+                                int64_t *p1_new, int b, int h, int w, int n, int fdim, int radius,
+                                int dilation_max, void *stream);
+
+/* Scalar parameters of the three GN residual models (union of the reference's scalar args,
+ * gn.h:22-117).  sigma_a/sigma_b: rays = (sigma_ray, sigma_dist); calib = (sigma_pixel,
+ * sigma_depth); points = (sigma_point, unused). */
+typedef struct {
+  int kind; /* B200SLAM_GN_* */
+  float sigma_a, sigma_b;
+  float C_thresh, Q_thresh;
+  int height, width, pixel_border; /* calib only */
+  float z_eps;                     /* calib only */
+} b200slam_gn_params;
+
+/* Bytes of device workspace the GN entry points need for N poses, E directed edges, n points. */
+size_t b200slam_gn_workspace_bytes(int N, int E, int n);
+
+/* One Hessian build in the reference's private buffer layout (gn_kernels.cu:1172-1194):
+ * Hs (4,E,7,7) f32 = [H_ii, H_ij, H_ji, H_jj] per edge, gs (2,E,7) f32 = [g_i, g_j].
+ * Twc (N,8) f32 [t, q xyzw, s]; Xs (N,n,3); Cs (N,n); K (3,3) or NULL; ii_row/jj_row (E) i64 are
+ * ROWS into Twc/Xs/Cs (the reference's ii_edge/jj_edge, :1161-1163); idx (E,n) i64;
+ * valid (E,n) u8; Q (E,n) f32.  Edges [e0, e0+Ecount) only (edge sharding); Hs/gs are indexed
+ * by the global edge number, extent E. */
+int b200slam_gn_build_blocks(const b200slam_gn_params *prm, const float *Twc, const float *Xs,
+                             const float *Cs, const float *K, const int64_t *ii_row,
+                             const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                             const float *Q, int N, int E, int n, int e0, int Ecount, float *Hs,
+                             float *gs, void *workspace, size_t workspace_bytes, void *stream);
+
+/* Stage 1+2 of one iteration for edges [e0,e0+Ecount): per-edge reduced blocks in fp64,
+ * edge_blocks (E,56) f64 = [H_jj (49, row-major) | g_j (7)] (H_ii = H_jj, H_ij = H_ji = -H_jj,
+ * g_i = -g_j; gn_kernels.cu:998-999).  Rows outside the shard are left untouched, so a
+ * zero-initialised buffer can be summed across ranks with one allreduce. */
+int b200slam_gn_edge_blocks(const b200slam_gn_params *prm, const float *Twc, const float *Xs,
+                            const float *Cs, const float *K, const int64_t *ii_row,
+                            const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                            const float *Q, int N, int E, int n, int e0, int Ecount,
+                            double *edge_blocks, void *workspace, size_t workspace_bytes,
+                            void *stream);
+
+/* Stage 3: assemble the 7(N-1) normal equations from edge_blocks (num_fix = 1, fixed rows
+ * skipped, duplicates summed: SparseBlock::update_lhs/rhs, gn_kernels.cu:70-112), fp64
+ * Cholesky solve (zero update when not SPD, :141-149), dx = -x (:1208), in-place Sim3
+ * retraction of Twc rows >= 1 (pose_retr_kernel, :414-452), and the ||dx|| < delta test
+ * (:1218-1221) recorded in the workspace so later iterations become no-ops.  dx (N-1,7) f32. */
+int b200slam_gn_solve_retract(float *Twc, const int64_t *ii_row, const int64_t *jj_row,
+                              const double *edge_blocks, int N, int E, int n, float delta_thresh,
+                              float *dx, void *workspace, size_t workspace_bytes, void *stream);
+
+/* Reset the iteration state (done flag, iteration counter) kept at the head of the workspace. */
+int b200slam_gn_reset(void *workspace, size_t workspace_bytes, void *stream);
+/* Read back {iterations executed, done flag, cholesky failures} (synchronises the stream). */
+int b200slam_gn_status(const void *workspace, int *iters, int *done, int *chol_fail, void *stream);
+
+/* Whole driver: replaces gauss_newton_{rays,calib,points}_cuda (gn_kernels.cu:1139-1227,
+ * :1545-1637, :724-810) for a single GPU.  Enqueues max_iter iterations with no host
+ * synchronisation; iterations after convergence are skipped on the device.  Twc is updated in
+ * place; dx (N-1,7) f32 receives the last update. */
+int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, const float *Xs,
+                          const float *Cs, const float *K, const int64_t *ii_row,
+                          const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                          const float *Q, int N, int E, int n, int max_iter, float delta_thresh,
+                          float *dx, void *workspace, size_t workspace_bytes, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200SLAM_H */

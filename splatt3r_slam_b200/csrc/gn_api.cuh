@@ -1,0 +1,213 @@
+// b200slam — C-ABI entry points of the Gauss-Newton path (declared in include/b200slam.h).
+#pragma once
+
+namespace b200gn {
+
+inline BuildConsts make_consts(const b200slam_gn_params *p, const float *Kdev_host_copy) {
+  BuildConsts C;
+  C.sa_inv = 1.0f / p->sigma_a;
+  C.sb_inv = 1.0f / p->sigma_b;
+  C.C_thresh = p->C_thresh;
+  C.Q_thresh = p->Q_thresh;
+  C.fx = Kdev_host_copy[0]; C.fy = Kdev_host_copy[4]; C.cx = Kdev_host_copy[2]; C.cy = Kdev_host_copy[5];
+  C.z_eps = p->z_eps;
+  C.ulo = (float)p->pixel_border;
+  C.uhi = (float)(p->width - 1 - p->pixel_border);
+  C.vlo = (float)p->pixel_border;
+  C.vhi = (float)(p->height - 1 - p->pixel_border);
+  C.width = p->width > 0 ? p->width : 1;
+  return C;
+}
+
+// K lives on the device (it is a torch CUDA tensor in the reference).  The 4 intrinsics are
+// fetched once per call with a small D2H copy; callers that want a fully asynchronous call
+// can pass K == NULL for the rays/points models.
+inline int fetch_K(const b200slam_gn_params *p, const float *K, float *Kh, cudaStream_t st) {
+  for (int i = 0; i < 9; i++) Kh[i] = 0.0f;
+  if (p->kind == B200SLAM_GN_CALIB) {
+    if (!K) return B200SLAM_EINVAL;
+    cudaError_t err = cudaMemcpyAsync(Kh, K, 9 * sizeof(float), cudaMemcpyDeviceToHost, st);
+    if (err != cudaSuccess) return (int)err;
+    err = cudaStreamSynchronize(st);
+    if (err != cudaSuccess) return (int)err;
+  }
+  return 0;
+}
+
+inline int launch_build(const b200slam_gn_params *p, const BuildConsts &C, const float *Twc,
+                        const float *Xs, const float *Cs, const int64_t *ii_row, const int64_t *jj_row,
+                        const int64_t *idx, const uint8_t *valid, const float *Q, int n, int e0,
+                        int Ecount, int S, double *partials, const State *state, cudaStream_t st) {
+  if (Ecount <= 0) return 0;
+  dim3 grid(S, Ecount);
+  switch (p->kind) {
+    case B200SLAM_GN_RAYS:
+      build_kernel<B200SLAM_GN_RAYS><<<grid, BUILD_THREADS, 0, st>>>(Twc, Xs, Cs, ii_row, jj_row, idx, valid,
+                                                                    Q, n, e0, C, partials, state);
+      break;
+    case B200SLAM_GN_CALIB:
+      build_kernel<B200SLAM_GN_CALIB><<<grid, BUILD_THREADS, 0, st>>>(Twc, Xs, Cs, ii_row, jj_row, idx,
+                                                                     valid, Q, n, e0, C, partials, state);
+      break;
+    case B200SLAM_GN_POINTS:
+      build_kernel<B200SLAM_GN_POINTS><<<grid, BUILD_THREADS, 0, st>>>(Twc, Xs, Cs, ii_row, jj_row, idx,
+                                                                      valid, Q, n, e0, C, partials, state);
+      break;
+    default:
+      return B200SLAM_EINVAL;
+  }
+  return (int)cudaGetLastError();
+}
+
+inline int launch_edge_blocks(const b200slam_gn_params *p, const BuildConsts &C, const float *Twc,
+                              const float *Xs, const float *Cs, const int64_t *ii_row,
+                              const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                              const float *Q, int E, int n, int e0, int Ecount, double *edge_blocks,
+                              char *ws, const Layout &L, cudaStream_t st) {
+  State *state = reinterpret_cast<State *>(ws);
+  double *partials = reinterpret_cast<double *>(ws + L.partials);
+  int rc = launch_build(p, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, e0, Ecount, L.S, partials,
+                        state, st);
+  if (rc) return rc;
+  if (Ecount > 0) {
+    const int warps_per_cta = 4;
+    finalize_kernel<<<(Ecount + warps_per_cta - 1) / warps_per_cta, 32 * warps_per_cta, 0, st>>>(
+        Twc, ii_row, partials, L.S, e0, Ecount, edge_blocks, state);
+    rc = (int)cudaGetLastError();
+  }
+  return rc;
+}
+
+inline int launch_solve(float *Twc, const int64_t *ii_row, const int64_t *jj_row,
+                        const double *edge_blocks, int N, int E, float delta_thresh, float *dx, char *ws,
+                        const Layout &L, cudaStream_t st) {
+  State *state = reinterpret_cast<State *>(ws);
+  double *A = reinterpret_cast<double *>(ws + L.A), *rhs = reinterpret_cast<double *>(ws + L.rhs);
+  const int M = N - NUM_FIX, D = 7 * M, Dp = D < 32 ? 32 : D;
+  assemble_kernel<<<M, 256, 0, st>>>(ii_row, jj_row, edge_blocks, E, D, A, rhs, state);
+  int rc = (int)cudaGetLastError();
+  if (rc) return rc;
+  if (D <= PACKED_MAX_D) {
+    const size_t smem = (size_t)(2 * Dp + (size_t)D * (D + 1) / 2) * sizeof(double);
+    static bool attr_set = false;
+    if (!attr_set) {
+      cudaFuncSetAttribute(solve_retract_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      attr_set = true;
+    }
+    solve_retract_kernel<true><<<1, SOLVE_THREADS, smem, st>>>(Twc, A, rhs, N, D, Dp, delta_thresh, dx, state);
+  } else {
+    const size_t smem = (size_t)2 * Dp * sizeof(double);
+    if (smem > 200 * 1024) return B200SLAM_EINVAL;
+    static bool attr_set2 = false;
+    if (!attr_set2) {
+      cudaFuncSetAttribute(solve_retract_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      attr_set2 = true;
+    }
+    solve_retract_kernel<false><<<1, SOLVE_THREADS, smem, st>>>(Twc, A, rhs, N, D, Dp, delta_thresh, dx, state);
+  }
+  return (int)cudaGetLastError();
+}
+
+inline bool bad_args(const b200slam_gn_params *p, const void *Twc, const void *Xs, const void *Cs,
+                     const void *ii, const void *jj, const void *idx, const void *valid, const void *Q,
+                     int N, int E, int n, const void *ws) {
+  return !p || !Twc || !Xs || !Cs || !ii || !jj || !idx || !valid || !Q || !ws || N < 1 || E < 0 || n < 0 ||
+         p->kind < 0 || p->kind > 2;
+}
+
+}  // namespace b200gn
+
+using namespace b200gn;
+
+extern "C" size_t b200slam_gn_workspace_bytes(int N, int E, int n) { return make_layout(N, E, n).total; }
+
+extern "C" int b200slam_gn_reset(void *workspace, size_t workspace_bytes, void *stream) {
+  if (!workspace || workspace_bytes < STATE_BYTES) return B200SLAM_EWORKSPACE;
+  return (int)cudaMemsetAsync(workspace, 0, STATE_BYTES, (cudaStream_t)stream);
+}
+
+extern "C" int b200slam_gn_status(const void *workspace, int *iters, int *done, int *chol_fail, void *stream) {
+  if (!workspace) return B200SLAM_EINVAL;
+  State h;
+  cudaError_t err = cudaMemcpyAsync(&h, workspace, sizeof(State), cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+  if (err != cudaSuccess) return (int)err;
+  err = cudaStreamSynchronize((cudaStream_t)stream);
+  if (err != cudaSuccess) return (int)err;
+  if (iters) *iters = h.iters;
+  if (done) *done = h.done;
+  if (chol_fail) *chol_fail = h.chol_fail;
+  return 0;
+}
+
+extern "C" int b200slam_gn_edge_blocks(const b200slam_gn_params *prm, const float *Twc, const float *Xs,
+                                       const float *Cs, const float *K, const int64_t *ii_row,
+                                       const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                                       const float *Q, int N, int E, int n, int e0, int Ecount,
+                                       double *edge_blocks, void *workspace, size_t workspace_bytes,
+                                       void *stream) {
+  if (bad_args(prm, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, N, E, n, workspace) || !edge_blocks ||
+      e0 < 0 || Ecount < 0 || e0 + Ecount > E)
+    return B200SLAM_EINVAL;
+  const Layout L = make_layout(N, E, n);
+  if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  float Kh[9];
+  int rc = fetch_K(prm, K, Kh, st);
+  if (rc) return rc;
+  const BuildConsts C = make_consts(prm, Kh);
+  return launch_edge_blocks(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, E, n, e0, Ecount,
+                            edge_blocks, (char *)workspace, L, st);
+}
+
+extern "C" int b200slam_gn_build_blocks(const b200slam_gn_params *prm, const float *Twc, const float *Xs,
+                                        const float *Cs, const float *K, const int64_t *ii_row,
+                                        const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                                        const float *Q, int N, int E, int n, int e0, int Ecount, float *Hs,
+                                        float *gs, void *workspace, size_t workspace_bytes, void *stream) {
+  if (!Hs || !gs) return B200SLAM_EINVAL;
+  const Layout L = make_layout(N, E, n);
+  if (!workspace || workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
+  double *eb = reinterpret_cast<double *>((char *)workspace + L.edge_blocks);
+  int rc = b200slam_gn_edge_blocks(prm, Twc, Xs, Cs, K, ii_row, jj_row, idx, valid, Q, N, E, n, e0, Ecount,
+                                   eb, workspace, workspace_bytes, stream);
+  if (rc || Ecount == 0) return rc;
+  export_blocks_kernel<<<(Ecount * 56 + 255) / 256, 256, 0, (cudaStream_t)stream>>>(eb, E, e0, Ecount, Hs, gs);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200slam_gn_solve_retract(float *Twc, const int64_t *ii_row, const int64_t *jj_row,
+                                         const double *edge_blocks, int N, int E, int n, float delta_thresh,
+                                         float *dx, void *workspace, size_t workspace_bytes, void *stream) {
+  if (!Twc || !ii_row || !jj_row || !edge_blocks || !dx || !workspace || N < 2 || E < 0) return B200SLAM_EINVAL;
+  const Layout L = make_layout(N, E, n);
+  if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
+  return launch_solve(Twc, ii_row, jj_row, edge_blocks, N, E, delta_thresh, dx, (char *)workspace, L,
+                      (cudaStream_t)stream);
+}
+
+extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, const float *Xs,
+                                     const float *Cs, const float *K, const int64_t *ii_row,
+                                     const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                                     const float *Q, int N, int E, int n, int max_iter, float delta_thresh,
+                                     float *dx, void *workspace, size_t workspace_bytes, void *stream) {
+  if (bad_args(prm, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, N, E, n, workspace) || !dx || N < 2)
+    return B200SLAM_EINVAL;
+  const Layout L = make_layout(N, E, n);
+  if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  char *ws = (char *)workspace;
+  float Kh[9];
+  int rc = fetch_K(prm, K, Kh, st);
+  if (rc) return rc;
+  const BuildConsts C = make_consts(prm, Kh);
+  rc = (int)cudaMemsetAsync(ws, 0, STATE_BYTES, st);
+  if (rc) return rc;
+  double *eb = reinterpret_cast<double *>(ws + L.edge_blocks);
+  for (int it = 0; it < max_iter; it++) {
+    rc = launch_edge_blocks(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, E, n, 0, E, eb, ws, L, st);
+    if (rc) return rc;
+    rc = launch_solve(Twc, ii_row, jj_row, eb, N, E, delta_thresh, dx, ws, L, st);
+    if (rc) return rc;
+  }
+  return 0;
+}

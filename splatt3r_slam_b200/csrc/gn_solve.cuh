@@ -1,0 +1,226 @@
+// b200slam — stage 3 of a GN iteration: deterministic assembly of the normal equations,
+// fp64 Cholesky, back-substitution, Sim3 retraction and the convergence flag, all on the device.
+// Replaces SparseBlock (gn_kernels.cu:56-158: host-side Eigen SimplicialLLT<double>),
+// pose_retr_kernel (:414-452) and the host-side ||dx|| test (:1218-1221).
+#pragma once
+
+namespace b200gn {
+
+constexpr int NUM_FIX = 1;  // gn_kernels.cu:1156
+
+// One CTA per free pose r: zero its 7 x D strip of A, then add every incident edge block in
+// edge order (fixed order => deterministic, no atomics).  Mirrors update_lhs/update_rhs
+// (:70-112): blocks with a fixed pose (index < 0) are skipped, duplicates are summed.
+__global__ void __launch_bounds__(256)
+assemble_kernel(const int64_t *__restrict__ ii_row, const int64_t *__restrict__ jj_row,
+                const double *__restrict__ edge_blocks, int E, int D, double *__restrict__ A,
+                double *__restrict__ rhs, const State *__restrict__ state) {
+  if (state->done) return;
+  const int r = blockIdx.x;
+  double *strip = A + (size_t)7 * r * D;
+  for (int t = threadIdx.x; t < 7 * D; t += blockDim.x) strip[t] = 0.0;
+  __syncthreads();
+  const int t = threadIdx.x;
+  if (t < 56) {
+    const int k = t / 7, l = t % 7;  // t in [49,56): rhs component l
+    double accb = 0.0;
+    for (int e = 0; e < E; e++) {
+      const int i = (int)ii_row[e] - NUM_FIX, j = (int)jj_row[e] - NUM_FIX;
+      if (i != r && j != r) continue;
+      const double v = edge_blocks[(size_t)e * 56 + t];
+      if (t < 49) {
+        if (i == r) {
+          strip[(size_t)k * D + 7 * i + l] += v;
+          if (j >= 0) strip[(size_t)k * D + 7 * j + l] -= v;
+        }
+        if (j == r) {
+          strip[(size_t)k * D + 7 * j + l] += v;
+          if (i >= 0) strip[(size_t)k * D + 7 * i + l] -= v;
+        }
+      } else {
+        if (i == r) accb -= v;  // g_i = -g_j
+        if (j == r) accb += v;
+      }
+    }
+    if (t >= 49) rhs[7 * r + l] = accb;
+  }
+}
+
+// ---- Sim3 exponential / retraction (expSO3 :298-320, expSim3 :322-389, retrSim3 :391-412) -----
+__device__ inline void retract_pose(float *p, const float *xi) {
+  const float tau[3] = {xi[0], xi[1], xi[2]}, phi[3] = {xi[3], xi[4], xi[5]}, sigma = xi[6];
+  const float scale = expf(sigma);
+  const float theta_sq = phi[0] * phi[0] + phi[1] * phi[1] + phi[2] * phi[2];
+  const float theta = sqrtf(theta_sq);
+  float imag, real;
+  if (theta_sq < 1e-6f) {
+    const float p4 = theta_sq * theta_sq;
+    imag = 0.5f - (1.0f / 48.0f) * theta_sq + (1.0f / 3840.0f) * p4;
+    real = 1.0f - (1.0f / 8.0f) * theta_sq + (1.0f / 384.0f) * p4;
+  } else {
+    imag = sinf(0.5f * theta) / theta;
+    real = cosf(0.5f * theta);
+  }
+  const float dq[4] = {imag * phi[0], imag * phi[1], imag * phi[2], real};
+  float A, B, C;
+  if (fabsf(sigma) < 1e-6f) {
+    C = 1.0f;
+    if (fabsf(theta) < 1e-6f) {
+      A = 0.5f;
+      B = 1.0f / 6.0f;
+    } else {
+      A = (1.0f - cosf(theta)) / theta_sq;
+      B = (theta - sinf(theta)) / (theta_sq * theta);
+    }
+  } else {
+    C = (scale - 1.0f) / sigma;
+    if (fabsf(theta) < 1e-6f) {
+      const float s2 = sigma * sigma;
+      A = ((sigma - 1.0f) * scale + 1.0f) / s2;
+      B = (scale * 0.5f * s2 + scale - 1.0f - sigma * scale) / (s2 * sigma);
+    } else {
+      const float a = scale * sinf(theta), b = scale * cosf(theta), c = theta_sq + sigma * sigma;
+      A = (a * sigma + (1.0f - b) * theta) / (theta * c);
+      B = (C - ((b - 1.0f) * sigma + a * theta) / c) / theta_sq;
+    }
+  }
+  // dt = (C I + A [phi]x + B [phi]x^2) tau
+  const float c1[3] = {phi[1] * tau[2] - phi[2] * tau[1], phi[2] * tau[0] - phi[0] * tau[2],
+                       phi[0] * tau[1] - phi[1] * tau[0]};
+  const float c2[3] = {phi[1] * c1[2] - phi[2] * c1[1], phi[2] * c1[0] - phi[0] * c1[2],
+                       phi[0] * c1[1] - phi[1] * c1[0]};
+  const float dt[3] = {C * tau[0] + A * c1[0] + B * c2[0], C * tau[1] + A * c1[1] + B * c2[1],
+                       C * tau[2] + A * c1[2] + B * c2[2]};
+  // T <- Exp(xi) * T   (left composition)
+  const float q[4] = {p[3], p[4], p[5], p[6]};
+  float t1[3];
+  rotate(dq, p, t1);
+  p[0] = t1[0] * scale + dt[0];
+  p[1] = t1[1] * scale + dt[1];
+  p[2] = t1[2] * scale + dt[2];
+  p[3] = dq[3] * q[0] + dq[0] * q[3] + dq[1] * q[2] - dq[2] * q[1];
+  p[4] = dq[3] * q[1] - dq[0] * q[2] + dq[1] * q[3] + dq[2] * q[0];
+  p[5] = dq[3] * q[2] + dq[0] * q[1] - dq[1] * q[0] + dq[2] * q[3];
+  p[6] = dq[3] * q[3] - dq[0] * q[0] - dq[1] * q[1] - dq[2] * q[2];
+  p[7] = scale * p[7];
+}
+
+// Lower-triangular storage accessors: packed in shared memory (small systems) or the full
+// row-major matrix in global memory.
+struct PackedLower {
+  double *p;
+  __device__ __forceinline__ double &at(int i, int k) const { return p[(size_t)i * (i + 1) / 2 + k]; }
+};
+struct FullLower {
+  double *p;
+  int D;
+  __device__ __forceinline__ double &at(int i, int k) const { return p[(size_t)i * D + k]; }
+};
+
+// Right-looking Cholesky + two triangular solves by ONE CTA.  Returns false when a pivot is
+// not positive (the reference's "solver.info() != Success" => dx = 0, :141-149).
+// x (length D, shared) holds the rhs on entry and the solution on exit; col is scratch (D).
+template <class Mat>
+__device__ bool cholesky_solve(Mat L, int D, double *x, double *col, int *fail) {
+  const int tid = threadIdx.x, T = blockDim.x;
+  const int lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
+  if (tid == 0) *fail = 0;
+  __syncthreads();
+  for (int j = 0; j < D; j++) {
+    if (tid == 0) {
+      const double d = L.at(j, j);
+      if (!(d > 0.0)) *fail = 1;
+      else L.at(j, j) = sqrt(d);
+    }
+    __syncthreads();
+    if (*fail) return false;
+    const double dinv = 1.0 / L.at(j, j);
+    for (int i = j + 1 + tid; i < D; i += T) {
+      const double v = L.at(i, j) * dinv;
+      L.at(i, j) = v;
+      col[i] = v;
+    }
+    __syncthreads();
+    // trailing update: row i (one warp per row), k over lanes
+    for (int i = j + 1 + warp; i < D; i += nwarp) {
+      const double ci = col[i];
+      for (int k = j + 1 + lane; k <= i; k += 32) L.at(i, k) -= ci * col[k];
+    }
+    __syncthreads();
+  }
+  // forward: L y = b
+  for (int j = 0; j < D; j++) {
+    if (tid == 0) x[j] = x[j] / L.at(j, j);
+    __syncthreads();
+    const double yj = x[j];
+    for (int i = j + 1 + tid; i < D; i += T) x[i] -= L.at(i, j) * yj;
+    __syncthreads();
+  }
+  // backward: L^T x = y
+  for (int j = D - 1; j >= 0; j--) {
+    if (tid == 0) x[j] = x[j] / L.at(j, j);
+    __syncthreads();
+    const double xj = x[j];
+    for (int i = tid; i < j; i += T) x[i] -= L.at(j, i) * xj;
+    __syncthreads();
+  }
+  return true;
+}
+
+constexpr int SOLVE_THREADS = 1024;
+constexpr int PACKED_MAX_D = 217;  // 217*218/2*8 = 189 KB of packed lower triangle in smem
+
+// dynamic smem: [x: Dp][col: Dp][packed L: D(D+1)/2 if PACKED]
+template <bool PACKED>
+__global__ void __launch_bounds__(SOLVE_THREADS)
+solve_retract_kernel(float *__restrict__ Twc, double *__restrict__ A, const double *__restrict__ rhs,
+                     int N, int D, int Dp, float delta_thresh, float *__restrict__ dx, State *state) {
+  if (state->done) return;
+  extern __shared__ double sm[];
+  double *x = sm, *col = sm + Dp;  // Dp = max(D, 32): col doubles as the cross-warp scratch
+  __shared__ int fail;
+  __shared__ double nrm2;
+  const int tid = threadIdx.x;
+  for (int i = tid; i < D; i += blockDim.x) x[i] = rhs[i];
+  bool ok;
+  if (PACKED) {
+    PackedLower L{sm + 2 * Dp};
+    for (int i = 0; i < D; i++)
+      for (int k = tid; k <= i; k += blockDim.x) L.at(i, k) = A[(size_t)i * D + k];
+    __syncthreads();
+    ok = cholesky_solve(L, D, x, col, &fail);
+  } else {
+    FullLower L{A, D};
+    __syncthreads();
+    ok = cholesky_solve(L, D, x, col, &fail);
+  }
+  // dx = -x (f32), zeros on failure;  ||dx||_2 in the reference is taken on the f32 tensor
+  if (tid == 0) nrm2 = 0.0;
+  __syncthreads();
+  double part = 0.0;
+  for (int i = tid; i < D; i += blockDim.x) {
+    const float v = ok ? -(float)x[i] : 0.0f;
+    dx[i] = v;
+    part += (double)v * (double)v;
+  }
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  __syncthreads();
+  // deterministic cross-warp sum
+  double *wsum = col;
+  if ((tid & 31) == 0) wsum[tid >> 5] = part;
+  __syncthreads();
+  if (tid == 0) {
+    double s = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); w++) s += wsum[w];
+    nrm2 = s;
+  }
+  __syncthreads();
+  for (int k = NUM_FIX + tid; k < N; k += blockDim.x) retract_pose(Twc + 8 * k, dx + 7 * (k - NUM_FIX));
+  if (tid == 0) {
+    state->iters += 1;
+    if (!ok) state->chol_fail += 1;
+    if ((float)sqrt(nrm2) < delta_thresh) state->done = 1;
+  }
+}
+
+}  // namespace b200gn

@@ -1,0 +1,213 @@
+"""Drop-in replacement for the reference's `mast3r_slam_backends` extension module.
+
+Same five functions, positional signatures, return lists, dtypes/layouts and in-place
+semantics as the reference's pybind module (splatt3r_slam/backend/src/gn.cpp:116-123,
+include/gn.h:22-117), so `matching.py:60,79` and `global_opt.py:140,190` of the reference run
+unchanged on top of it.  This layer only checks arguments, allocates outputs, remaps
+keyframe ids to rows (gn_kernels.cu:160-169) and forwards raw device pointers + the current
+CUDA stream to the C ABI in libb200slam.so (include/b200slam.h).  There is NO CPU fallback:
+importing works without a GPU (so the symbol table can be checked), calling does not.
+"""
+import ctypes
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB_PATH = os.path.join(_HERE, "libb200slam.so")
+
+GN_RAYS, GN_CALIB, GN_POINTS = 0, 1, 2
+
+
+class GNParams(ctypes.Structure):
+    _fields_ = [("kind", ctypes.c_int), ("sigma_a", ctypes.c_float), ("sigma_b", ctypes.c_float),
+                ("C_thresh", ctypes.c_float), ("Q_thresh", ctypes.c_float), ("height", ctypes.c_int),
+                ("width", ctypes.c_int), ("pixel_border", ctypes.c_int), ("z_eps", ctypes.c_float)]
+
+
+def _load():
+    if not os.path.exists(_LIB_PATH):
+        raise ImportError(
+            f"{_LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(nvcc, sm_100a).  There is no CPU fallback for this backend.")
+    lib = ctypes.CDLL(_LIB_PATH)
+    vp, i, f, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_size_t
+    P = ctypes.POINTER(GNParams)
+    lib.b200slam_version.restype = i
+    lib.b200slam_iter_proj.argtypes = [vp] * 5 + [i] * 5 + [f, f, vp]
+    lib.b200slam_refine_matches_f16.argtypes = [vp] * 4 + [i] * 7 + [vp]
+    lib.b200slam_refine_matches_f32.argtypes = [vp] * 4 + [i] * 7 + [vp]
+    lib.b200slam_gn_workspace_bytes.argtypes = [i, i, i]
+    lib.b200slam_gn_workspace_bytes.restype = sz
+    lib.b200slam_gn_build_blocks.argtypes = [P] + [vp] * 9 + [i] * 5 + [vp, vp, vp, sz, vp]
+    lib.b200slam_gn_edge_blocks.argtypes = [P] + [vp] * 9 + [i] * 5 + [vp, vp, sz, vp]
+    lib.b200slam_gn_solve_retract.argtypes = [vp] * 4 + [i, i, i, f, vp, vp, sz, vp]
+    lib.b200slam_gn_reset.argtypes = [vp, sz, vp]
+    lib.b200slam_gn_status.argtypes = [vp, ctypes.POINTER(i), ctypes.POINTER(i), ctypes.POINTER(i), vp]
+    lib.b200slam_gauss_newton.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
+    for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "gn_build_blocks",
+                 "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gauss_newton"):
+        getattr(lib, "b200slam_" + name).restype = i
+    return lib
+
+
+_lib = _load()
+EXPORTS = ("gauss_newton_points", "gauss_newton_rays", "gauss_newton_calib", "iter_proj", "refine_matches")
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise RuntimeError(f"b200slam {what} failed with code {rc}")
+
+
+def _contig(**tensors):
+    # gn.h:5 CHECK_CONTIGUOUS -> RuntimeError("<name> must be contiguous")
+    for name, t in tensors.items():
+        if not t.is_contiguous():
+            raise RuntimeError(f"{name} must be contiguous")
+
+
+def _cuda(t, dtype, name):
+    if not t.is_cuda:
+        raise RuntimeError(f"{name} must be a CUDA tensor (this backend has no CPU path)")
+    if t.dtype != dtype:
+        raise RuntimeError(f"expected scalar type {dtype} for {name} but found {t.dtype}")
+    return t.data_ptr()
+
+
+def _stream(t):
+    return torch.cuda.current_stream(t.device).cuda_stream
+
+
+def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, cost_thresh):
+    _contig(rays_img_with_grad=rays_img_with_grad, pts_3d_norm=pts_3d_norm, p_init=p_init)
+    b, h, w, c = rays_img_with_grad.shape
+    if c != 9:
+        raise RuntimeError("rays_img_with_grad must have 9 channels (ray, d/du, d/dv)")
+    n = p_init.shape[1]
+    with torch.cuda.device(p_init.device):
+        p_new = torch.empty((b, n, 2), dtype=torch.float32, device=p_init.device)
+        conv = torch.empty((b, n), dtype=torch.bool, device=p_init.device)
+        _check(_lib.b200slam_iter_proj(
+            _cuda(rays_img_with_grad, torch.float32, "rays_img_with_grad"),
+            _cuda(pts_3d_norm, torch.float32, "pts_3d_norm"), _cuda(p_init, torch.float32, "p_init"),
+            p_new.data_ptr(), conv.data_ptr(), b, h, w, n, int(max_iter), float(lambda_init),
+            float(cost_thresh), _stream(p_init)), "iter_proj")
+    return [p_new, conv]
+
+
+def refine_matches(D11, D21, p1, radius, dilation_max):
+    _contig(D11=D11, D21=D21, p1=p1)
+    b, h, w, fdim = D11.shape
+    n = p1.shape[1]
+    with torch.cuda.device(p1.device):
+        p1_new = torch.empty((b, n, 2), dtype=torch.int64, device=p1.device)
+        if D11.dtype == torch.float16:
+            fn = _lib.b200slam_refine_matches_f16
+        elif D11.dtype == torch.float32:
+            fn = _lib.b200slam_refine_matches_f32
+        else:
+            raise RuntimeError(f"refine_matches: unsupported descriptor dtype {D11.dtype}")
+        _check(fn(_cuda(D11, D11.dtype, "D11"), _cuda(D21, D11.dtype, "D21"), _cuda(p1, torch.int64, "p1"),
+                  p1_new.data_ptr(), b, h, w, n, fdim, int(radius), int(dilation_max), _stream(p1)),
+               "refine_matches")
+    return [p1_new]
+
+
+def edge_rows(ii, jj):
+    """Keyframe ids -> rows of Twc/Xs/Cs: dense rank among the sorted unique ids
+    (reference: torch::_unique + searchsorted, gn_kernels.cu:160-169).  No host sync."""
+    E = ii.numel()
+    s, order = torch.sort(torch.cat([ii, jj]))
+    rank_sorted = torch.cumsum(torch.cat([s.new_zeros(1), (s[1:] != s[:-1]).to(s.dtype)]), 0)
+    rows = torch.empty_like(rank_sorted)
+    rows[order] = rank_sorted
+    return rows[:E].contiguous(), rows[E:].contiguous()
+
+
+_workspaces = {}
+
+
+def _workspace(device, nbytes):
+    key = (device.type, device.index)
+    ws = _workspaces.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+        _workspaces[key] = ws
+    return ws
+
+
+def _gn_ptrs(Twc, Xs, Cs, K, ii_row, jj_row, idx, valid, Q):
+    return (_cuda(Twc, torch.float32, "Twc"), _cuda(Xs, torch.float32, "Xs"), _cuda(Cs, torch.float32, "Cs"),
+            (_cuda(K, torch.float32, "K") if K is not None else None), ii_row.data_ptr(), jj_row.data_ptr(),
+            _cuda(idx, torch.int64, "idx_ii2jj"), _cuda(valid, torch.bool, "valid_match"),
+            _cuda(Q, torch.float32, "Q"))
+
+
+def _gauss_newton(prm, Twc, Xs, Cs, K, ii, jj, idx, valid, Q, max_iter, delta_thresh):
+    _contig(Twc=Twc, Xs=Xs, Cs=Cs, ii=ii, jj=jj, idx_ii2jj=idx, valid_match=valid, Q=Q)
+    if K is not None:
+        _contig(K=K)
+    N, n = Xs.shape[0], Xs.shape[1]
+    E = ii.shape[0]
+    if max_iter <= 0 or N < 2 or E == 0:
+        return [torch.zeros((max(N - 1, 0), 7), dtype=torch.float32, device=Twc.device)]
+    with torch.cuda.device(Twc.device):
+        _cuda(ii, torch.int64, "ii"), _cuda(jj, torch.int64, "jj")
+        ii_row, jj_row = edge_rows(ii, jj)
+        dx = torch.zeros((N - 1, 7), dtype=torch.float32, device=Twc.device)
+        nbytes = _lib.b200slam_gn_workspace_bytes(N, E, n)
+        ws = _workspace(Twc.device, nbytes)
+        _check(_lib.b200slam_gauss_newton(
+            ctypes.byref(prm), *_gn_ptrs(Twc, Xs, Cs, K, ii_row, jj_row, idx, valid, Q), N, E, n,
+            int(max_iter), float(delta_thresh), dx.data_ptr(), ws.data_ptr(), nbytes, _stream(Twc)),
+            "gauss_newton")
+    return [dx]
+
+
+def gauss_newton_rays(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_ray, sigma_dist, C_thresh,
+                      Q_thresh, max_iter, delta_thresh):
+    prm = GNParams(GN_RAYS, sigma_ray, sigma_dist, C_thresh, Q_thresh, 0, 0, 0, 0.0)
+    return _gauss_newton(prm, Twc, Xs, Cs, None, ii, jj, idx_ii2jj, valid_match, Q, max_iter, delta_thresh)
+
+
+def gauss_newton_calib(Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, height, width, pixel_border,
+                       z_eps, sigma_pixel, sigma_depth, C_thresh, Q_thresh, max_iter, delta_thresh):
+    prm = GNParams(GN_CALIB, sigma_pixel, sigma_depth, C_thresh, Q_thresh, int(height), int(width),
+                   int(pixel_border), z_eps)
+    return _gauss_newton(prm, Twc, Xs, Cs, K, ii, jj, idx_ii2jj, valid_match, Q, max_iter, delta_thresh)
+
+
+def gauss_newton_points(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_point, C_thresh, Q_thresh,
+                        max_iter, delta_thresh):
+    prm = GNParams(GN_POINTS, sigma_point, 1.0, C_thresh, Q_thresh, 0, 0, 0, 0.0)
+    return _gauss_newton(prm, Twc, Xs, Cs, None, ii, jj, idx_ii2jj, valid_match, Q, max_iter, delta_thresh)
+
+
+# ---- extras beyond the reference module (used by tests, bench and the multi-GPU driver) ----------
+def make_params(kind, sigma_a, sigma_b, C_thresh, Q_thresh, height=0, width=0, pixel_border=0, z_eps=0.0):
+    return GNParams(kind, sigma_a, sigma_b, C_thresh, Q_thresh, int(height), int(width), int(pixel_border), z_eps)
+
+
+def gn_build_blocks(prm, Twc, Xs, Cs, K, ii, jj, idx, valid, Q):
+    """One Hessian build in the reference's private layout: Hs (4,E,7,7), gs (2,E,7) fp32."""
+    N, n, E = Xs.shape[0], Xs.shape[1], ii.shape[0]
+    with torch.cuda.device(Twc.device):
+        ii_row, jj_row = edge_rows(ii, jj)
+        Hs = torch.zeros((4, E, 7, 7), dtype=torch.float32, device=Twc.device)
+        gs = torch.zeros((2, E, 7), dtype=torch.float32, device=Twc.device)
+        nbytes = _lib.b200slam_gn_workspace_bytes(N, E, n)
+        ws = _workspace(Twc.device, nbytes)
+        _check(_lib.b200slam_gn_reset(ws.data_ptr(), nbytes, _stream(Twc)), "gn_reset")
+        _check(_lib.b200slam_gn_build_blocks(
+            ctypes.byref(prm), *_gn_ptrs(Twc, Xs, Cs, K, ii_row, jj_row, idx, valid, Q), N, E, n, 0, E,
+            Hs.data_ptr(), gs.data_ptr(), ws.data_ptr(), nbytes, _stream(Twc)), "gn_build_blocks")
+    return Hs, gs
+
+
+def gn_status(device):
+    ws = _workspaces[(device.type, device.index)]
+    it, dn, cf = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
+    _check(_lib.b200slam_gn_status(ws.data_ptr(), ctypes.byref(it), ctypes.byref(dn), ctypes.byref(cf),
+                                   torch.cuda.current_stream(device).cuda_stream), "gn_status")
+    return dict(iters=it.value, done=dn.value, chol_fail=cf.value)

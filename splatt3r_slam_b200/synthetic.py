@@ -1,0 +1,163 @@
+"""Seeded synthetic inputs of MASt3R shape for the backend hot path.
+
+Everything is generated on the CPU with a torch.Generator so that the same seed gives the same
+tensors here and on the GPU box; callers move the result to the device.
+
+Scene: a smooth height field z = f(x, y) in the world frame, observed by pinhole cameras
+(fx = fy = 500*w/512, principal point at the image centre) placed at seeded Sim3 poses
+[t(3), q xyzw(4), s(1)] (the lietorch layout the reference stores in `T_WC.data`).
+"""
+import math
+
+import torch
+
+
+def _quat_from_axis_angle(v):
+    th = v.norm(dim=-1, keepdim=True).clamp_min(1e-12)
+    return torch.cat([torch.sin(0.5 * th) * v / th, torch.cos(0.5 * th)], dim=-1)
+
+
+def quat_rotate(q, X):
+    qv, qw = q[..., :3], q[..., 3:]
+    uv = 2.0 * torch.cross(qv.expand_as(X), X, dim=-1)
+    return X + qw * uv + torch.cross(qv.expand_as(X), uv, dim=-1)
+
+
+def sim3_act(T, X):
+    """T (...,8) acting on X (...,3): s*R*X + t"""
+    return T[..., 7:8] * quat_rotate(T[..., 3:7], X) + T[..., 0:3]
+
+
+def sim3_inv_act(T, X):
+    q = T[..., 3:7] * torch.tensor([-1.0, -1.0, -1.0, 1.0], dtype=T.dtype)
+    return quat_rotate(q, X - T[..., 0:3]) / T[..., 7:8]
+
+
+def random_pose(gen, rot_deg=5.0, trans=0.1, scale=0.05):
+    axis = torch.randn(3, generator=gen, dtype=torch.float64)
+    axis = axis / axis.norm()
+    ang = math.radians(rot_deg) * (2 * torch.rand(1, generator=gen, dtype=torch.float64) - 1)
+    q = _quat_from_axis_angle(axis * ang)
+    t = trans * (2 * torch.rand(3, generator=gen, dtype=torch.float64) - 1)
+    s = 1.0 + scale * (2 * torch.rand(1, generator=gen, dtype=torch.float64) - 1)
+    return torch.cat([t, q, s])
+
+
+class Scene:
+    def __init__(self, seed, h=384, w=512):
+        self.gen = torch.Generator().manual_seed(seed)
+        self.h, self.w = h, w
+        f = 500.0 * w / 512.0
+        self.K = torch.tensor([[f, 0, w / 2.0], [0, f, h / 2.0], [0, 0, 1]], dtype=torch.float64)
+        g = self.gen
+        self.freq = 0.5 + 2.5 * torch.rand(4, 2, generator=g, dtype=torch.float64)
+        self.phase = 2 * math.pi * torch.rand(4, generator=g, dtype=torch.float64)
+
+    def surf(self, x, y):
+        z = torch.full_like(x, 2.0)
+        for k in range(4):
+            z = z + 0.125 * torch.sin(self.freq[k, 0] * x + self.freq[k, 1] * y + self.phase[k])
+        return z
+
+    def raycast(self, T):
+        """World points (h,w,3) hit by the pixel rays of the camera at Sim3 pose T (fp64)."""
+        h, w, K = self.h, self.w, self.K
+        v, u = torch.meshgrid(torch.arange(h, dtype=torch.float64), torch.arange(w, dtype=torch.float64),
+                              indexing="ij")
+        d_cam = torch.stack([(u - K[0, 2]) / K[0, 0], (v - K[1, 2]) / K[1, 1], torch.ones_like(u)], -1)
+        d = quat_rotate(T[3:7], d_cam)  # world direction (scale folded into the ray parameter)
+        o = T[0:3]
+        t = torch.full((h, w), 2.0, dtype=torch.float64)
+        for _ in range(8):
+            P = o + t[..., None] * d
+            t = t + (self.surf(P[..., 0], P[..., 1]) - P[..., 2]) / d[..., 2]
+        return o + t[..., None] * d
+
+    def project(self, T, Pw):
+        """World points -> (u, v, z) in the camera at pose T."""
+        Pc = sim3_inv_act(T, Pw)
+        z = Pc[..., 2]
+        u = self.K[0, 0] * Pc[..., 0] / z + self.K[0, 2]
+        v = self.K[1, 1] * Pc[..., 1] / z + self.K[1, 2]
+        return u, v, z
+
+
+def _descriptors(Pw, fdim, W, noise, gen):
+    feat = torch.cat([torch.sin(3.0 * Pw), torch.cos(3.0 * Pw), Pw], dim=-1)  # (...,9)
+    D = feat @ W + noise * torch.randn(*Pw.shape[:-1], fdim, generator=gen, dtype=torch.float64)
+    return D / D.norm(dim=-1, keepdim=True)
+
+
+def make_pair(seed=0, h=384, w=512, fdim=24, b=1, noise=0.005):
+    """One matcher call's inputs: X11, X21 (b,h,w,3), D11, D21 (b,h,w,fdim), all fp32.
+    View 1 is the identity camera; X21 are the points seen by a second camera at a seeded
+    Sim3 offset, expressed in camera 1 (what the asymmetric MASt3R head emits)."""
+    X11, X21, D11, D21 = [], [], [], []
+    for i in range(b):
+        sc = Scene(seed * 1000 + i, h, w)
+        g = sc.gen
+        W = torch.randn(9, fdim, generator=g, dtype=torch.float64)
+        T1 = torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float64)
+        T2 = random_pose(g)
+        P1, P2 = sc.raycast(T1), sc.raycast(T2)
+        X11.append(P1 + noise * torch.randn(h, w, 3, generator=g, dtype=torch.float64))
+        X21.append(P2 + noise * torch.randn(h, w, 3, generator=g, dtype=torch.float64))
+        D11.append(_descriptors(P1, fdim, W, 0.1, g))
+        D21.append(_descriptors(P2, fdim, W, 0.1, g))
+    f = lambda L: torch.stack(L).float().contiguous()
+    return f(X11), f(X21), f(D11), f(D21)
+
+
+def make_graph(seed=0, N=2, E_undirected=1, h=384, w=512, noise=0.005, pose_noise=0.01,
+               extra_edges="random"):
+    """A keyframe graph in the layout `global_opt.py:104-139` hands to the backend.
+
+    Returns dict with Twc (N,8) [perturbed], Twc_gt, Xs (N,n,3), Cs (N,n,1), K (3,3),
+    ii, jj (E,) int64 keyframe ids, idx_ii2jj (E,n) int64, valid_match (E,n,1) bool,
+    Q (E,n,1) fp32, with E = 2*E_undirected directed edges (both directions).
+    Edges: ring (k,k+1) first, then seeded random chords."""
+    sc = Scene(seed, h, w)
+    g = sc.gen
+    n = h * w
+    poses = [torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float64)]
+    for k in range(1, N):
+        poses.append(random_pose(g, rot_deg=6.0, trans=0.15, scale=0.05))
+    Tgt = torch.stack(poses)
+    Pw = [sc.raycast(Tgt[k]) for k in range(N)]
+    Xs = torch.stack([sim3_inv_act(Tgt[k], Pw[k]).reshape(n, 3) for k in range(N)])
+    Xs = Xs + noise * torch.randn(N, n, 3, generator=g, dtype=torch.float64)
+    Cs = 1.0 + torch.exp(0.5 * torch.randn(N, n, 1, generator=g, dtype=torch.float64))
+    und = [(k, (k + 1) % N) for k in range(min(N - 1 if N == 2 else N, E_undirected))]
+    while len(und) < E_undirected:
+        a, b_ = torch.randint(0, N, (2,), generator=g).tolist()
+        if a != b_:
+            und.append((a, b_))
+    ii = torch.tensor([a for a, _ in und] + [b_ for _, b_ in und], dtype=torch.int64)
+    jj = torch.tensor([b_ for _, b_ in und] + [a for a, _ in und], dtype=torch.int64)
+    E = ii.numel()
+    idx = torch.zeros(E, n, dtype=torch.int64)
+    valid = torch.zeros(E, n, 1, dtype=torch.bool)
+    for e in range(E):
+        i, j = int(ii[e]), int(jj[e])
+        u, v, z = sc.project(Tgt[i], Pw[j].reshape(n, 3))
+        ui, vi = torch.round(u).long(), torch.round(v).long()
+        ok = (ui >= 0) & (ui < w) & (vi >= 0) & (vi < h) & (z > 0)
+        idx[e] = torch.where(ok, ui.clamp(0, w - 1) + w * vi.clamp(0, h - 1), torch.zeros_like(ui))
+        valid[e, :, 0] = ok
+    Q = 1.0 + torch.exp(0.5 * torch.randn(E, n, 1, generator=g, dtype=torch.float64))
+    # perturb the free poses (left-multiplicative small Sim3 step; pose 0 is the gauge)
+    T = Tgt.clone()
+    for k in range(1, N):
+        d = random_pose(g, rot_deg=math.degrees(pose_noise), trans=pose_noise, scale=pose_noise)
+        t = d[7] * quat_rotate(d[3:7], T[k, 0:3]) + d[0:3]
+        qd, q = d[3:7], T[k, 3:7]
+        qn = torch.stack([
+            qd[3] * q[0] + qd[0] * q[3] + qd[1] * q[2] - qd[2] * q[1],
+            qd[3] * q[1] - qd[0] * q[2] + qd[1] * q[3] + qd[2] * q[0],
+            qd[3] * q[2] + qd[0] * q[1] - qd[1] * q[0] + qd[2] * q[3],
+            qd[3] * q[3] - qd[0] * q[0] - qd[1] * q[1] - qd[2] * q[2]])
+        T[k] = torch.cat([t, qn, (d[7] * T[k, 7]).reshape(1)])
+    return dict(Twc=T.float().contiguous(), Twc_gt=Tgt.float(), Xs=Xs.float().contiguous(),
+                Cs=Cs.float().contiguous(), K=sc.K.float().contiguous(), ii=ii, jj=jj,
+                idx_ii2jj=idx.contiguous(), valid_match=valid.contiguous(),
+                Q=Q.float().contiguous(), h=h, w=w)
