@@ -1,0 +1,198 @@
+"""GPU arms of bench.py (kept separate so `bench.py --impl reference` never touches CUDA)."""
+import json
+import os
+import time
+
+import torch
+import torch.distributed as dist
+
+from bench import (B_GN_EDGE, B_GN_POINT, B_ITER_PROJ, B_REFINE, FDIM, GN, H, N_PIX, W, ClockSampler, make_sets,
+                   peaks)
+
+
+def _init_dist(args):
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1 and not dist.is_initialized():
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    return rank, world, local
+
+
+def _barrier(world):
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+
+
+def _max_over_ranks(x, world, dev):
+    t = torch.tensor([x], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item()
+
+
+def cpu_baseline_tracker():
+    """Oracle (C port of the reference's CUDA-only algorithm) on the host cores, bounded sample."""
+    import oracle
+    from splatt3r_slam_b200 import matching
+    cores = os.cpu_count()
+    s = make_sets(1, 1000)[0]
+    rays, pts, p_init = matching.prep_for_iter_proj(s["X11"], s["X21"], None)
+    D11h, D21h = s["D11"].half(), s["D21"].view(1, N_PIX, -1).half().contiguous()
+    cfg = matching.DEFAULT_CFG
+    t0 = time.perf_counter()
+    p_new, _ = oracle.iter_proj(rays, pts, p_init, cfg["max_iter"], cfg["lambda_init"], cfg["convergence_thresh"])
+    oracle.refine_matches(D11h, D21h, p_new.long(), cfg["radius"], cfg["dilation_max"])
+    T = s["Twc"].clone()
+    oracle.gauss_newton_rays(T, s["Xs"], s["Cs"], s["ii"], s["jj"], s["idx_ii2jj"], s["valid_match"], s["Q"],
+                             GN["sigma_ray"], GN["sigma_dist"], GN["C_thresh"], GN["Q_thresh"], GN["iters"], 0.0)
+    dt = time.perf_counter() - t0
+    return {"value": N_PIX / dt, "unit": "px/s", "cores": cores, "kind": "port",
+            "sample": "one full tracker step (1 pair 512x384, iter_proj+refine+10 GN iters), OpenMP over all host threads"}
+
+
+def run_tracker(args):
+    rank, world, local = _init_dist(args)
+    dev = torch.device("cuda", local)
+    from splatt3r_slam_b200 import matching
+    import splatt3r_slam_b200.mast3r_slam_backends as be
+    cfg = matching.DEFAULT_CFG
+    n_sets = 6  # 6 x ~56 MB of distinct inputs > 126 MB L2: every step streams from HBM
+    host = make_sets(n_sets, 100 * (rank + 1))
+    sets = []
+    for s in host:
+        d = {k: v.to(dev) for k, v in s.items()}
+        rays, pts, p_init = matching.prep_for_iter_proj(d["X11"], d["X21"], None)
+        d.update(rays=rays, pts=pts, p_init=p_init, D11h=d["D11"].half().contiguous(),
+                 D21h=d["D21"].view(1, N_PIX, -1).half().contiguous())
+        sets.append(d)
+    ev = lambda: torch.cuda.Event(enable_timing=True)
+
+    def step(d):
+        p_new, conv = be.iter_proj(d["rays"], d["pts"], d["p_init"], cfg["max_iter"], cfg["lambda_init"],
+                                   cfg["convergence_thresh"])
+        p1 = p_new.long()
+        (p1r,) = be.refine_matches(d["D11h"], d["D21h"], p1, cfg["radius"], cfg["dilation_max"])
+        T = d["Twc"].clone()
+        be.gauss_newton_rays(T, d["Xs"], d["Cs"], d["ii"], d["jj"], d["idx_ii2jj"], d["valid_match"], d["Q"],
+                             GN["sigma_ray"], GN["sigma_dist"], GN["C_thresh"], GN["Q_thresh"], GN["iters"], 0.0)
+        return p1r, T
+
+    for i in range(args.warmup):
+        step(sets[i % n_sets])
+    # ---- timed region 1: device-resident inputs ("value") ------------------------------------
+    sampler = ClockSampler(local)
+    sampler.start()
+    _barrier(world)
+    t_a, t_b = ev(), ev()
+    t_a.record()
+    for i in range(args.steps):
+        step(sets[i % n_sets])
+    t_b.record()
+    _barrier(world)
+    ms = _max_over_ranks(t_a.elapsed_time(t_b), world, dev)
+    # ---- per-kernel durations (separate pass so the events do not perturb the headline) -------
+    kt = _kernel_times(be, cfg, sets, args.steps)
+    # ---- timed region 2: end to end from pinned host buffers ("e2e") --------------------------
+    pin = [{k: v.pin_memory() for k, v in s.items()} for s in host]
+    keys_match = ("X11", "X21", "D11", "D21")
+    keys_gn = ("Twc", "Xs", "Cs", "ii", "jj", "idx_ii2jj", "valid_match", "Q")
+    h2d = sum(pin[0][k].numel() * pin[0][k].element_size() for k in keys_match + keys_gn)
+    out_idx = torch.empty((1, N_PIX), dtype=torch.int64).pin_memory()
+    out_val = torch.empty((1, N_PIX, 1), dtype=torch.bool).pin_memory()
+    out_T = torch.empty((2, 8), dtype=torch.float32).pin_memory()
+    d2h = out_idx.numel() * 8 + out_val.numel() + out_T.numel() * 4
+
+    def e2e_step(p):
+        d = {k: p[k].to(dev, non_blocking=True) for k in keys_match + keys_gn}
+        idx, valid = matching.match(d["X11"], d["X21"], d["D11"], d["D21"], backend=be)
+        be.gauss_newton_rays(d["Twc"], d["Xs"], d["Cs"], d["ii"], d["jj"], d["idx_ii2jj"], d["valid_match"], d["Q"],
+                             GN["sigma_ray"], GN["sigma_dist"], GN["C_thresh"], GN["Q_thresh"], GN["iters"], 0.0)
+        out_idx.copy_(idx, non_blocking=True)
+        out_val.copy_(valid, non_blocking=True)
+        out_T.copy_(d["Twc"], non_blocking=True)
+
+    for i in range(max(3, args.warmup)):
+        e2e_step(pin[i % n_sets])
+    _barrier(world)
+    t_c, t_d = ev(), ev()
+    t_c.record()
+    for i in range(args.steps):
+        e2e_step(pin[i % n_sets])
+    t_d.record()
+    _barrier(world)
+    ms_e2e = _max_over_ranks(t_c.elapsed_time(t_d), world, dev)
+    sampler.stop_flag = True
+    sampler.join(timeout=2)
+
+    if rank != 0:
+        return
+    peak, peak_src = peaks()
+    dom = max(kt, key=lambda k: kt[k])
+    alg = {"iter_proj": B_ITER_PROJ * N_PIX, "refine": B_REFINE * N_PIX,
+           "gn": GN["iters"] * 2 * (B_GN_POINT * N_PIX + B_GN_EDGE)}
+    roof = {k: alg[k] / (kt[k] * 1e-6) / 1e9 for k in kt}
+    line = {
+        "metric": "matched_px_per_s", "value": world * N_PIX * args.steps / (ms * 1e-3), "unit": "px/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": "tracker step 512x384 24-d: iter_proj+refine_matches (b=1) + gauss_newton_rays N=2 E=2 10 iters",
+                   "l2": f"{n_sets} rotating input sets of ~56 MB (> 126 MB L2)", "ranks": "independent pairs per rank, no collective"},
+        "e2e": {"value": world * N_PIX * args.steps / (ms_e2e * 1e-3), "unit": "px/s", "h2d_bytes_per_step": h2d,
+                "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
+        "gpu_launches": args.steps * (2 + 4 * GN["iters"]),
+        "kernel_us": {k: round(v, 2) for k, v in kt.items()},
+        "match_px_per_s": N_PIX / ((kt["iter_proj"] + kt["refine"]) * 1e-6),
+        "gn_iters_per_s": {"E2": GN["iters"] / (kt["gn"] * 1e-6)},
+        "roofline": {"bound": "hbm", "kernel": dom, "achieved": roof[dom], "peak": peak, "unit": "GB/s",
+                     "frac": roof[dom] / peak, "traffic": None, "peak_source": peak_src,
+                     "all_kernels_GBps": {k: round(v, 1) for k, v in roof.items()}},
+        "clocks": sampler.result(),
+    }
+    if not args.no_cpu_baseline and world == 1:
+        line["cpu_baseline"] = cpu_baseline_tracker()
+    print(json.dumps(line))
+
+
+def _kernel_times(be, cfg, sets, steps):
+    """Average duration (us) of each backend call, CUDA events on the launching stream, inputs
+    rotating through the distinct sets (cold in L2)."""
+    n_sets = len(sets)
+    p1s = []
+    for d in sets:
+        p_new, _ = be.iter_proj(d["rays"], d["pts"], d["p_init"], cfg["max_iter"], cfg["lambda_init"],
+                                cfg["convergence_thresh"])
+        p1s.append(p_new.long())
+    Ts = [d["Twc"].clone() for d in sets]
+    fns = {
+        "iter_proj": lambda i: be.iter_proj(sets[i]["rays"], sets[i]["pts"], sets[i]["p_init"], cfg["max_iter"],
+                                            cfg["lambda_init"], cfg["convergence_thresh"]),
+        "refine": lambda i: be.refine_matches(sets[i]["D11h"], sets[i]["D21h"], p1s[i], cfg["radius"], cfg["dilation_max"]),
+        "gn": lambda i: (Ts[i].copy_(sets[i]["Twc"]),
+                         be.gauss_newton_rays(Ts[i], sets[i]["Xs"], sets[i]["Cs"], sets[i]["ii"], sets[i]["jj"],
+                                              sets[i]["idx_ii2jj"], sets[i]["valid_match"], sets[i]["Q"], GN["sigma_ray"],
+                                              GN["sigma_dist"], GN["C_thresh"], GN["Q_thresh"], GN["iters"], 0.0)),
+    }
+    out = {}
+    for name, fn in fns.items():
+        for i in range(3):
+            fn(i % n_sets)
+        torch.cuda.synchronize()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(steps):
+            fn(i % n_sets)
+        b.record()
+        torch.cuda.synchronize()
+        out[name] = a.elapsed_time(b) / steps * 1e3
+    return out
+
+
+def run_graph(args):
+    from splatt3r_slam_b200.dist_gn import bench_graph
+    rank, world, local = _init_dist(args)
+    line = bench_graph(args, rank, world, local)
+    if rank == 0:
+        print(json.dumps(line))

@@ -85,13 +85,13 @@ def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, co
     if c != 9:
         raise RuntimeError("rays_img_with_grad must have 9 channels (ray, d/du, d/dv)")
     n = p_init.shape[1]
+    ptrs = (_cuda(rays_img_with_grad, torch.float32, "rays_img_with_grad"),
+            _cuda(pts_3d_norm, torch.float32, "pts_3d_norm"), _cuda(p_init, torch.float32, "p_init"))
     with torch.cuda.device(p_init.device):
         p_new = torch.empty((b, n, 2), dtype=torch.float32, device=p_init.device)
         conv = torch.empty((b, n), dtype=torch.bool, device=p_init.device)
         _check(_lib.b200slam_iter_proj(
-            _cuda(rays_img_with_grad, torch.float32, "rays_img_with_grad"),
-            _cuda(pts_3d_norm, torch.float32, "pts_3d_norm"), _cuda(p_init, torch.float32, "p_init"),
-            p_new.data_ptr(), conv.data_ptr(), b, h, w, n, int(max_iter), float(lambda_init),
+            *ptrs, p_new.data_ptr(), conv.data_ptr(), b, h, w, n, int(max_iter), float(lambda_init),
             float(cost_thresh), _stream(p_init)), "iter_proj")
     return [p_new, conv]
 
@@ -100,16 +100,16 @@ def refine_matches(D11, D21, p1, radius, dilation_max):
     _contig(D11=D11, D21=D21, p1=p1)
     b, h, w, fdim = D11.shape
     n = p1.shape[1]
+    if D11.dtype == torch.float16:
+        fn = _lib.b200slam_refine_matches_f16
+    elif D11.dtype == torch.float32:
+        fn = _lib.b200slam_refine_matches_f32
+    else:
+        raise RuntimeError(f"refine_matches: unsupported descriptor dtype {D11.dtype}")
+    ptrs = (_cuda(D11, D11.dtype, "D11"), _cuda(D21, D11.dtype, "D21"), _cuda(p1, torch.int64, "p1"))
     with torch.cuda.device(p1.device):
         p1_new = torch.empty((b, n, 2), dtype=torch.int64, device=p1.device)
-        if D11.dtype == torch.float16:
-            fn = _lib.b200slam_refine_matches_f16
-        elif D11.dtype == torch.float32:
-            fn = _lib.b200slam_refine_matches_f32
-        else:
-            raise RuntimeError(f"refine_matches: unsupported descriptor dtype {D11.dtype}")
-        _check(fn(_cuda(D11, D11.dtype, "D11"), _cuda(D21, D11.dtype, "D21"), _cuda(p1, torch.int64, "p1"),
-                  p1_new.data_ptr(), b, h, w, n, fdim, int(radius), int(dilation_max), _stream(p1)),
+        _check(fn(*ptrs, p1_new.data_ptr(), b, h, w, n, fdim, int(radius), int(dilation_max), _stream(p1)),
                "refine_matches")
     return [p1_new]
 
@@ -150,6 +150,7 @@ def _gauss_newton(prm, Twc, Xs, Cs, K, ii, jj, idx, valid, Q, max_iter, delta_th
         _contig(K=K)
     N, n = Xs.shape[0], Xs.shape[1]
     E = ii.shape[0]
+    _cuda(Twc, torch.float32, "Twc")
     if max_iter <= 0 or N < 2 or E == 0:
         return [torch.zeros((max(N - 1, 0), 7), dtype=torch.float32, device=Twc.device)]
     with torch.cuda.device(Twc.device):

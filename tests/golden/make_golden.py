@@ -49,7 +49,7 @@ def main(out_dir):
     p1 = p_new.long()
     D11h, D21h = D11.half(), D21.view(2, h * w, -1).half().contiguous()
     (p1_ref,) = ref.refine_matches(D11h, D21h, p1, cfg["radius"], cfg["dilation_max"])
-    (p1_ref_f32,) = ref.refine_matches(D11.float(), D21.view(2, h * w, -1).float().contiguous(), p1,
+    (p1_ref_f32,) = ref.refine_matches(D11h.float(), D21h.float(), p1,  # fp32 kernel on the fp16-rounded values
                                        cfg["radius"], cfg["dilation_max"])
     torch.cuda.synchronize()
     np.savez_compressed(

@@ -1,0 +1,160 @@
+"""GPU tier: Gauss-Newton path through the drop-in module (-> C ABI -> sm_100a kernels) against
+the golden fixtures of the reference CUDA build, the C oracle, and the reference build itself
+when present.  Tolerance: 1e-5 relative (BASELINE.json north_star, fp32)."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from conftest import GOLDEN
+from splatt3r_slam_b200 import synthetic
+
+pytestmark = pytest.mark.gpu
+RTOL = 1e-5
+GN = dict(sigma_ray=0.003, sigma_dist=10.0, sigma_pixel=1.0, sigma_depth=10.0, sigma_point=0.05,
+          C_thresh=0.0, Q_thresh=1.5, pixel_border=-10, z_eps=1e-6)
+
+
+def dev():
+    return torch.device("cuda:0")
+
+
+def T(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(dev())
+
+
+def rel(a, b):
+    return ((a - b).abs().max() / b.abs().max()).item()
+
+
+def params(be, name, h, w):
+    if name == "rays":
+        return be.make_params(0, GN["sigma_ray"], GN["sigma_dist"], GN["C_thresh"], GN["Q_thresh"])
+    if name == "calib":
+        return be.make_params(1, GN["sigma_pixel"], GN["sigma_depth"], GN["C_thresh"], GN["Q_thresh"], h, w,
+                              GN["pixel_border"], GN["z_eps"])
+    return be.make_params(2, GN["sigma_point"], 1.0, GN["C_thresh"], GN["Q_thresh"])
+
+
+def run(be_mod, name, Twc, G, h, w, iters, delta):
+    if name == "rays":
+        return be_mod.gauss_newton_rays(Twc, G["Xs"], G["Cs"], G["ii"], G["jj"], G["idx_ii2jj"], G["valid_match"],
+                                        G["Q"], GN["sigma_ray"], GN["sigma_dist"], GN["C_thresh"], GN["Q_thresh"],
+                                        iters, delta)
+    if name == "calib":
+        return be_mod.gauss_newton_calib(Twc, G["Xs"], G["Cs"], G["K"], G["ii"], G["jj"], G["idx_ii2jj"],
+                                         G["valid_match"], G["Q"], h, w, GN["pixel_border"], GN["z_eps"],
+                                         GN["sigma_pixel"], GN["sigma_depth"], GN["C_thresh"], GN["Q_thresh"],
+                                         iters, delta)
+    return be_mod.gauss_newton_points(Twc, G["Xs"], G["Cs"], G["ii"], G["jj"], G["idx_ii2jj"], G["valid_match"],
+                                      G["Q"], GN["sigma_point"], GN["C_thresh"], GN["Q_thresh"], iters, delta)
+
+
+@pytest.fixture(scope="module")
+def golden():
+    g = np.load(os.path.join(GOLDEN, "gn_3kf_64x48.npz"))
+    G = {k: T(g[k]) for k in ("Twc", "Xs", "Cs", "K", "ii", "jj", "idx_ii2jj", "valid_match", "Q")}
+    return g, G
+
+
+@pytest.mark.parametrize("name", ["rays", "calib", "points"])
+def test_blocks_vs_golden(backend, golden, name):
+    g, G = golden
+    Hs, gs = backend.gn_build_blocks(params(backend, name, 48, 64), G["Twc"], G["Xs"], G["Cs"],
+                                     G["K"] if name == "calib" else None, G["ii"], G["jj"], G["idx_ii2jj"],
+                                     G["valid_match"], G["Q"])
+    Hr, gr = T(g[f"{name}_Hs"]), T(g[f"{name}_gs"])
+    for blk in range(4):
+        assert rel(Hs[blk], Hr[blk]) < RTOL
+    for blk in range(2):
+        assert rel(gs[blk], gr[blk]) < RTOL
+
+
+@pytest.mark.parametrize("name", ["rays", "calib", "points"])
+@pytest.mark.parametrize("iters", [1, 4])
+def test_loop_vs_golden(backend, golden, name, iters):
+    g, G = golden
+    Twc = G["Twc"].clone()
+    (dx,) = run(backend, name, Twc, G, 48, 64, iters, 0.0)
+    assert rel(Twc, T(g[f"{name}_T{iters}"])) < RTOL
+    assert torch.equal(Twc[0], G["Twc"][0])  # gauge pose untouched (num_fix = 1)
+    assert dx.shape == (2, 7) and dx.dtype == torch.float32
+    assert backend.gn_status(dev())["iters"] == iters
+
+
+@pytest.mark.parametrize("N,Eu,h,w", [(2, 1, 96, 128), (6, 9, 46, 61), (32, 64, 24, 32), (40, 60, 24, 32)])
+@pytest.mark.parametrize("name", ["rays", "calib"])
+def test_vs_oracle_and_reference(backend, ref_backend, name, N, Eu, h, w):
+    """46x61 -> n = 2806 (n % 4 != 0: scalar tail path);  N = 32 -> 217 unknowns (largest packed
+    shared-memory Cholesky);  N = 40 -> 273 unknowns (global-memory Cholesky)."""
+    g = synthetic.make_graph(seed=N + Eu, N=N, E_undirected=Eu, h=h, w=w)
+    G = {k: (v.to(dev()) if torch.is_tensor(v) else v) for k, v in g.items()}
+    prm = params(backend, name, h, w)
+    Hs, gs = backend.gn_build_blocks(prm, G["Twc"], G["Xs"], G["Cs"], G["K"] if name == "calib" else None,
+                                     G["ii"], G["jj"], G["idx_ii2jj"], G["valid_match"], G["Q"])
+    Ho, go = oracle.gn_build(prm.kind, g["Twc"], g["Xs"], g["Cs"], g["K"] if name == "calib" else None, g["ii"],
+                             g["jj"], g["idx_ii2jj"], g["valid_match"], g["Q"], prm.sigma_a, prm.sigma_b,
+                             prm.C_thresh, prm.Q_thresh, prm.height, prm.width, prm.pixel_border, prm.z_eps)
+    for e in range(2 * Eu):  # per edge: every Hessian block within 1e-5 of that block's scale
+        assert rel(Hs[:, e].cpu(), Ho[:, e]) < RTOL, e
+        assert rel(gs[:, e].cpu(), go[:, e]) < 5 * RTOL, e
+    Tb = G["Twc"].clone()
+    run(backend, name, Tb, G, h, w, 5, 0.0)
+    To = g["Twc"].clone()
+    run(oracle, name, To, g, h, w, 5, 0.0)
+    assert (Tb.cpu() - To).abs().max().item() < 2e-5
+    if ref_backend is not None:
+        Tr = G["Twc"].clone()
+        run(ref_backend, name, Tr, G, h, w, 5, 0.0)
+        assert (Tb - Tr).abs().max().item() < 2e-5
+
+
+def test_early_exit_keeps_reference_iteration_count(backend, golden):
+    g, G = golden
+    # delta so large that the first update already satisfies ||dx|| < delta (gn_kernels.cu:1218-1221)
+    Twc = G["Twc"].clone()
+    run(backend, "rays", Twc, G, 48, 64, 10, 1e9)
+    st = backend.gn_status(dev())
+    assert st["iters"] == 1 and st["done"] == 1
+    assert rel(Twc, T(g["rays_T1"])) < RTOL
+    # realistic threshold: same number of iterations as the oracle's loop
+    g2 = synthetic.make_graph(seed=3, N=4, E_undirected=5, h=48, w=64)
+    G2 = {k: (v.to(dev()) if torch.is_tensor(v) else v) for k, v in g2.items()}
+    Tb, To = G2["Twc"].clone(), g2["Twc"].clone()
+    run(backend, "rays", Tb, G2, 48, 64, 30, 2e-5)
+    run(oracle, "rays", To, g2, 48, 64, 30, 2e-5)
+    assert abs(backend.gn_status(dev())["iters"] - oracle._gauss_newton.last_iters) <= 1
+    assert (Tb.cpu() - To).abs().max().item() < 5e-5
+
+
+def test_not_spd_gives_zero_update(backend, golden):
+    g, G = golden
+    Twc = G["Twc"].clone()
+    G0 = dict(G, valid_match=torch.zeros_like(G["valid_match"]))
+    (dx,) = run(backend, "rays", Twc, G0, 48, 64, 3, 1e-8)
+    st = backend.gn_status(dev())
+    assert torch.equal(Twc, G["Twc"]) and not dx.any()
+    assert st["chol_fail"] == 1 and st["iters"] == 1 and st["done"] == 1  # 0 < delta -> stop
+
+
+def test_keyframe_ids_are_remapped_like_unique_searchsorted(backend, golden):
+    g, G = golden
+    Ta = G["Twc"].clone()
+    run(backend, "rays", Ta, G, 48, 64, 2, 0.0)
+    remap = torch.tensor([17, 40, 123], device=dev())  # sparse, sorted ids -> same rows
+    Gb = dict(G, ii=remap[G["ii"]].contiguous(), jj=remap[G["jj"]].contiguous())
+    Tb = G["Twc"].clone()
+    run(backend, "rays", Tb, Gb, 48, 64, 2, 0.0)
+    assert torch.equal(Ta, Tb)
+
+
+def test_deterministic(backend, golden):
+    g, G = golden
+    outs = []
+    for _ in range(3):
+        Twc = G["Twc"].clone()
+        run(backend, "calib", Twc, G, 48, 64, 4, 0.0)
+        outs.append(Twc)
+    assert torch.equal(outs[0], outs[1]) and torch.equal(outs[0], outs[2])
