@@ -31,10 +31,15 @@ int b200slam_version(void);
 
 /* Replaces iter_proj_cuda / iter_proj_kernel, matching_kernels.cu:118-315 (pybind gn.cpp:84-99).
  * rays_img (b,h,w,9) f32; pts_3d_norm (b,n,3) f32; p_init (b,n,2) f32 (u,v)
- * -> p_new (b,n,2) f32; converged (b,n) u8 (torch.bool storage).  Bit-exact with the reference. */
+ * -> p_new (b,n,2) f32; converged (b,n) u8 (torch.bool storage).  Bit-exact with the reference.
+ * workspace: b200slam_iter_proj_workspace_bytes(b,h,w) bytes of device scratch (planar copy of
+ * the ray image: the kernel re-lays the 9 interleaved channels out as planes so that a warp's
+ * bilinear taps coalesce). */
+size_t b200slam_iter_proj_workspace_bytes(int b, int h, int w);
 int b200slam_iter_proj(const float *rays_img, const float *pts_3d_norm, const float *p_init,
                        float *p_new, uint8_t *converged, int b, int h, int w, int n, int max_iter,
-                       float lambda_init, float cost_thresh, void *stream);
+                       float lambda_init, float cost_thresh, void *workspace, size_t workspace_bytes,
+                       void *stream);
 
 /* Replaces refine_matches_cuda / refine_matches_kernel<c10::Half>, matching_kernels.cu:24-115
  * (pybind gn.cpp:101-114).  D11 (b,h,w,fdim) f16; D21 (b,n,fdim) f16; p1 (b,n,2) i64 (u,v)

@@ -18,7 +18,7 @@ struct State {  // head of the workspace
   int iters;      // iterations executed so far
   int done;       // set when ||dx|| < delta_thresh: later launches are no-ops
   int chol_fail;  // number of failed factorisations (dx = 0)
-  int pad;
+  unsigned ticket;  // arrival counter of the fused small-problem path (reset by the last CTA)
 };
 constexpr size_t STATE_BYTES = 256;
 constexpr int MAX_SPLITS = 296;
@@ -53,14 +53,20 @@ inline Layout make_layout(int N, int E, int n) {
   return L;
 }
 
+}  // namespace b200gn
+
+#include "gn_solve.cuh"
+
+namespace b200gn {
+
 // ---- stage 1 ----------------------------------------------------------------------------------
-template <int KIND>
+template <int KIND, bool FUSED>
 __global__ void __launch_bounds__(BUILD_THREADS)
-build_kernel(const float *__restrict__ Twc, const float *__restrict__ Xs, const float *__restrict__ Cs,
+build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__ Cs,
              const int64_t *__restrict__ ii_row, const int64_t *__restrict__ jj_row,
              const int64_t *__restrict__ idx, const uint8_t *__restrict__ valid,
-             const float *__restrict__ Q, int n, int e0, BuildConsts C, double *__restrict__ partials,
-             const State *__restrict__ state) {
+             const float *__restrict__ Q, int n, int e0, BuildConsts C, double *partials, State *state,
+             int N, int E, float delta_thresh, float *dx, double *edge_blocks) {
   if (state->done) return;
   const int e = e0 + blockIdx.y;
   const int S = gridDim.x, s = blockIdx.x;
@@ -77,7 +83,8 @@ build_kernel(const float *__restrict__ Twc, const float *__restrict__ Xs, const 
 #pragma unroll
   for (int l = 0; l < NACC; l++) acc[l] = 0.0f;
 
-  const int groups = n >> 2;  // groups of 4 points
+  const bool vec_ok = (n & 3) == 0;          // 16-byte loads need every edge row 16-byte aligned
+  const int groups = vec_ok ? (n >> 2) : 0;  // groups of 4 points
   const int gper = (groups + S - 1) / S;
   const int g_begin = s * gper, g_end = min(groups, g_begin + gper);
   for (int g = g_begin + threadIdx.x; g < g_end; g += BUILD_THREADS) {
@@ -108,9 +115,11 @@ build_kernel(const float *__restrict__ Twc, const float *__restrict__ Xs, const 
     for (int t = 0; t < 4; t++)
       if ((vm4 >> (8 * t)) & 0xffu) point_contrib<KIND>(acc, P, C, Xi[t], ci[t], Xj[t], cj[t], qq[t], ind[t]);
   }
-  // tail points (n % 4) handled by the last split, one point per thread
-  if (s == S - 1) {
-    for (int k = (groups << 2) + threadIdx.x; k < n; k += BUILD_THREADS) {
+  // scalar path (n % 4 != 0): the split takes a contiguous range of points, one per thread
+  if (!vec_ok) {
+    const int per = (n + S - 1) / S;
+    const int k_end = min(n, (s + 1) * per);
+    for (int k = s * per + threadIdx.x; k < k_end; k += BUILD_THREADS) {
       if (!val_e[k]) continue;
       const long long id = idx_e[k];
       const float Xi[3] = {Xi_base[3 * id], Xi_base[3 * id + 1], Xi_base[3 * id + 2]};
@@ -135,42 +144,21 @@ build_kernel(const float *__restrict__ Twc, const float *__restrict__ Xs, const 
     for (int wq = 0; wq < BUILD_THREADS / 32; wq++) sum += (double)red[wq][threadIdx.x];
     partials[((size_t)e * S + s) * NACC + threadIdx.x] = sum;
   }
+  if (FUSED) {
+    // last-arriving CTA finishes the iteration: finalize + assemble + solve + retract
+    __shared__ bool is_last;
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) is_last = atomicAdd(&state->ticket, 1u) == gridDim.x * gridDim.y - 1;
+    __syncthreads();
+    if (!is_last) return;
+    __threadfence();
+    if (threadIdx.x == 0) state->ticket = 0;
+    small_tail(Twc, ii_row, jj_row, partials, S, E, N, delta_thresh, dx, edge_blocks, state);
+  }
 }
 
-// ---- stage 2: per-edge reduce over splits + M^T H0 M in fp64 -----------------------------------
-// M rows = apply_Sim3_adj_inv(T_i) applied to unit vectors (gn_kernels.cu:276-296), in fp64.
-__device__ void adj_inv_matrix(const float *Ti, double (&M)[7][7]) {
-  const double t[3] = {Ti[0], Ti[1], Ti[2]}, q[4] = {Ti[3], Ti[4], Ti[5], Ti[6]};
-  const double s_inv = 1.0 / (double)Ti[7];
-  // rotation matrix of q (same formula as actSO3 expanded)
-  double R[3][3];
-  for (int c = 0; c < 3; c++) {
-    double X[3] = {0, 0, 0};
-    X[c] = 1.0;
-    const double uv0 = 2.0 * (q[1] * X[2] - q[2] * X[1]);
-    const double uv1 = 2.0 * (q[2] * X[0] - q[0] * X[2]);
-    const double uv2 = 2.0 * (q[0] * X[1] - q[1] * X[0]);
-    R[0][c] = X[0] + q[3] * uv0 + (q[1] * uv2 - q[2] * uv1);
-    R[1][c] = X[1] + q[3] * uv1 + (q[2] * uv0 - q[0] * uv2);
-    R[2][c] = X[2] + q[3] * uv2 + (q[0] * uv1 - q[1] * uv0);
-  }
-  for (int k = 0; k < 7; k++)
-    for (int c = 0; c < 7; c++) M[k][c] = 0.0;
-  for (int k = 0; k < 3; k++) {  // input component a_k: Ra = R[:,k]
-    const double Ra[3] = {R[0][k], R[1][k], R[2][k]};
-    M[k][0] = s_inv * Ra[0]; M[k][1] = s_inv * Ra[1]; M[k][2] = s_inv * Ra[2];
-    M[k][3] = s_inv * (t[1] * Ra[2] - t[2] * Ra[1]);
-    M[k][4] = s_inv * (t[2] * Ra[0] - t[0] * Ra[2]);
-    M[k][5] = s_inv * (t[0] * Ra[1] - t[1] * Ra[0]);
-    M[k][6] = s_inv * (t[0] * Ra[0] + t[1] * Ra[1] + t[2] * Ra[2]);
-  }
-  for (int k = 0; k < 3; k++) {  // input component b_k: Rb = R[:,k]
-    M[3 + k][3] = R[0][k]; M[3 + k][4] = R[1][k]; M[3 + k][5] = R[2][k];
-  }
-  M[6][6] = 1.0;
-}
-
-// one warp per edge; lanes cooperate on the 35 sums, lane 0 does the 7x7x7 transform
+// ---- stage 2 (large problems): one warp per edge -----------------------------------------------
 __global__ void __launch_bounds__(128)
 finalize_kernel(const float *__restrict__ Twc, const int64_t *__restrict__ ii_row,
                 const double *__restrict__ partials, int S, int e0, int Ecount,
@@ -178,41 +166,9 @@ finalize_kernel(const float *__restrict__ Twc, const int64_t *__restrict__ ii_ro
   if (state->done) return;
   const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (wid >= Ecount) return;
+  __shared__ double sc[4][FIN_SCRATCH];
   const int e = e0 + wid;
-  __shared__ double sh[4][2][NACC + 1];
-  double(&acc)[NACC + 1] = sh[(threadIdx.x >> 5)][0];
-  for (int l = lane; l < NACC; l += 32) {
-    double s = 0.0;
-    for (int k = 0; k < S; k++) s += partials[((size_t)e * S + k) * NACC + l];
-    acc[l] = s;
-  }
-  __syncwarp();
-  if (lane == 0) {
-    double M[7][7], H0[7][7], T[7][7];
-    adj_inv_matrix(Twc + 8 * (int)ii_row[e], M);
-    int l = 0;
-    for (int a = 0; a < 7; a++)
-      for (int b = a; b < 7; b++, l++) H0[a][b] = H0[b][a] = acc[l];
-    for (int a = 0; a < 7; a++)
-      for (int c = 0; c < 7; c++) {
-        double s = 0.0;
-        for (int k = 0; k < 7; k++) s += H0[a][k] * M[k][c];
-        T[a][c] = s;
-      }
-    double *out = edge_blocks + (size_t)e * 56;
-    for (int r = 0; r < 7; r++)
-      for (int c = r; c < 7; c++) {
-        double s = 0.0;
-        for (int k = 0; k < 7; k++) s += M[k][r] * T[k][c];
-        out[r * 7 + c] = s;
-        out[c * 7 + r] = s;
-      }
-    for (int r = 0; r < 7; r++) {
-      double s = 0.0;
-      for (int k = 0; k < 7; k++) s += M[k][r] * acc[28 + k];
-      out[49 + r] = s;
-    }
-  }
+  finalize_edge(Twc, ii_row, partials, S, e, edge_blocks + (size_t)e * 56, sc[threadIdx.x >> 5], lane);
 }
 
 // reference-layout export: Hs (4,E,7,7) f32, gs (2,E,7) f32 (gn_kernels.cu:1119-1132)
@@ -235,5 +191,4 @@ __global__ void export_blocks_kernel(const double *__restrict__ edge_blocks, int
 
 }  // namespace b200gn
 
-#include "gn_solve.cuh"
 #include "gn_api.cuh"

@@ -34,24 +34,46 @@ inline int fetch_K(const b200slam_gn_params *p, const float *K, float *Kh, cudaS
   return 0;
 }
 
+// Tail arguments of the fused small-problem path (ignored when fused == false).
+struct FusedArgs {
+  bool fused;
+  int N, E;
+  float delta_thresh;
+  float *dx;
+  double *edge_blocks;
+};
+
+template <int KIND>
+inline void launch_build_kind(dim3 grid, cudaStream_t st, const BuildConsts &C, float *Twc, const float *Xs,
+                              const float *Cs, const int64_t *ii_row, const int64_t *jj_row, const int64_t *idx,
+                              const uint8_t *valid, const float *Q, int n, int e0, double *partials, State *state,
+                              const FusedArgs &F) {
+  if (F.fused)
+    build_kernel<KIND, true><<<grid, BUILD_THREADS, 0, st>>>(Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, e0, C,
+                                                            partials, state, F.N, F.E, F.delta_thresh, F.dx,
+                                                            F.edge_blocks);
+  else
+    build_kernel<KIND, false><<<grid, BUILD_THREADS, 0, st>>>(Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, e0, C,
+                                                             partials, state, 0, 0, 0.0f, nullptr, nullptr);
+}
+
 inline int launch_build(const b200slam_gn_params *p, const BuildConsts &C, const float *Twc,
                         const float *Xs, const float *Cs, const int64_t *ii_row, const int64_t *jj_row,
                         const int64_t *idx, const uint8_t *valid, const float *Q, int n, int e0,
-                        int Ecount, int S, double *partials, const State *state, cudaStream_t st) {
+                        int Ecount, int S, double *partials, State *state, cudaStream_t st,
+                        const FusedArgs &F = FusedArgs{false, 0, 0, 0.0f, nullptr, nullptr}) {
   if (Ecount <= 0) return 0;
   dim3 grid(S, Ecount);
+  float *T = const_cast<float *>(Twc);  // written only by the fused tail
   switch (p->kind) {
     case B200SLAM_GN_RAYS:
-      build_kernel<B200SLAM_GN_RAYS><<<grid, BUILD_THREADS, 0, st>>>(Twc, Xs, Cs, ii_row, jj_row, idx, valid,
-                                                                    Q, n, e0, C, partials, state);
+      launch_build_kind<B200SLAM_GN_RAYS>(grid, st, C, T, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, e0, partials, state, F);
       break;
     case B200SLAM_GN_CALIB:
-      build_kernel<B200SLAM_GN_CALIB><<<grid, BUILD_THREADS, 0, st>>>(Twc, Xs, Cs, ii_row, jj_row, idx,
-                                                                     valid, Q, n, e0, C, partials, state);
+      launch_build_kind<B200SLAM_GN_CALIB>(grid, st, C, T, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, e0, partials, state, F);
       break;
     case B200SLAM_GN_POINTS:
-      build_kernel<B200SLAM_GN_POINTS><<<grid, BUILD_THREADS, 0, st>>>(Twc, Xs, Cs, ii_row, jj_row, idx,
-                                                                      valid, Q, n, e0, C, partials, state);
+      launch_build_kind<B200SLAM_GN_POINTS>(grid, st, C, T, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, e0, partials, state, F);
       break;
     default:
       return B200SLAM_EINVAL;
@@ -203,7 +225,15 @@ extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, 
   rc = (int)cudaMemsetAsync(ws, 0, STATE_BYTES, st);
   if (rc) return rc;
   double *eb = reinterpret_cast<double *>(ws + L.edge_blocks);
+  const bool fused = 7 * (N - NUM_FIX) <= SMALL_MAX_D && E <= SMALL_MAX_E;
   for (int it = 0; it < max_iter; it++) {
+    if (fused) {  // one launch per iteration: the last stage-1 CTA runs stages 2-3
+      const FusedArgs F{true, N, E, delta_thresh, dx, eb};
+      rc = launch_build(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, 0, E, L.S,
+                        reinterpret_cast<double *>(ws + L.partials), reinterpret_cast<State *>(ws), st, F);
+      if (rc) return rc;
+      continue;
+    }
     rc = launch_edge_blocks(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, E, n, 0, E, eb, ws, L, st);
     if (rc) return rc;
     rc = launch_solve(Twc, ii_row, jj_row, eb, N, E, delta_thresh, dx, ws, L, st);

@@ -8,6 +8,73 @@ namespace b200gn {
 
 constexpr int NUM_FIX = 1;  // gn_kernels.cu:1156
 
+// M rows = apply_Sim3_adj_inv(T_i) applied to unit vectors (gn_kernels.cu:276-296), in fp64,
+// row-major M[k*7+c]:  Jj = J0 * M.
+__device__ inline void adj_inv_matrix(const float *Ti, double *M) {
+  const double t[3] = {Ti[0], Ti[1], Ti[2]}, q[4] = {Ti[3], Ti[4], Ti[5], Ti[6]};
+  const double s_inv = 1.0 / (double)Ti[7];
+  double R[3][3];
+  for (int c = 0; c < 3; c++) {
+    double X[3] = {0, 0, 0};
+    X[c] = 1.0;
+    const double uv0 = 2.0 * (q[1] * X[2] - q[2] * X[1]);
+    const double uv1 = 2.0 * (q[2] * X[0] - q[0] * X[2]);
+    const double uv2 = 2.0 * (q[0] * X[1] - q[1] * X[0]);
+    R[0][c] = X[0] + q[3] * uv0 + (q[1] * uv2 - q[2] * uv1);
+    R[1][c] = X[1] + q[3] * uv1 + (q[2] * uv0 - q[0] * uv2);
+    R[2][c] = X[2] + q[3] * uv2 + (q[0] * uv1 - q[1] * uv0);
+  }
+  for (int k = 0; k < 49; k++) M[k] = 0.0;
+  for (int k = 0; k < 3; k++) {
+    const double Ra[3] = {R[0][k], R[1][k], R[2][k]};
+    M[k * 7 + 0] = s_inv * Ra[0]; M[k * 7 + 1] = s_inv * Ra[1]; M[k * 7 + 2] = s_inv * Ra[2];
+    M[k * 7 + 3] = s_inv * (t[1] * Ra[2] - t[2] * Ra[1]);
+    M[k * 7 + 4] = s_inv * (t[2] * Ra[0] - t[0] * Ra[2]);
+    M[k * 7 + 5] = s_inv * (t[0] * Ra[1] - t[1] * Ra[0]);
+    M[k * 7 + 6] = s_inv * (t[0] * Ra[0] + t[1] * Ra[1] + t[2] * Ra[2]);
+    M[(3 + k) * 7 + 3] = R[0][k]; M[(3 + k) * 7 + 4] = R[1][k]; M[(3 + k) * 7 + 5] = R[2][k];
+  }
+  M[48] = 1.0;
+}
+
+constexpr int FIN_SCRATCH = 36 + 49 + 49;  // doubles of shared scratch per warp
+
+// Warp-cooperative stage 2 for one edge: sum the S per-CTA partials in fixed order (fp64),
+// then H_jj = M^T H0 M and g_j = M^T g0 -> out[0..48], out[49..55].
+__device__ inline void finalize_edge(const float *Twc, const int64_t *ii_row, const double *partials, int S,
+                                     int e, double *out, double *sc, int lane) {
+  double *acc = sc, *M = sc + 36, *T = sc + 36 + 49;
+  for (int l = lane; l < NACC; l += 32) {
+    double s = 0.0;
+    for (int k = 0; k < S; k++) s += partials[((size_t)e * S + k) * NACC + l];
+    acc[l] = s;
+  }
+  if (lane == 0) adj_inv_matrix(Twc + 8 * (int)ii_row[e], M);
+  __syncwarp();
+  for (int o = lane; o < 49; o += 32) {
+    const int a = o / 7, c = o % 7;
+    double s = 0.0;
+    for (int k = 0; k < 7; k++) {
+      const int lo = a < k ? a : k, hi = a < k ? k : a;
+      s += acc[lo * 7 - lo * (lo - 1) / 2 + (hi - lo)] * M[k * 7 + c];
+    }
+    T[o] = s;
+  }
+  __syncwarp();
+  for (int o = lane; o < 56; o += 32) {
+    double s = 0.0;
+    if (o < 49) {
+      const int r = o / 7, c = o % 7;
+      for (int k = 0; k < 7; k++) s += M[k * 7 + r] * T[k * 7 + c];
+    } else {
+      const int r = o - 49;
+      for (int k = 0; k < 7; k++) s += M[k * 7 + r] * acc[28 + k];
+    }
+    out[o] = s;
+  }
+  __syncwarp();
+}
+
 // One CTA per free pose r: zero its 7 x D strip of A, then add every incident edge block in
 // edge order (fixed order => deterministic, no atomics).  Mirrors update_lhs/update_rhs
 // (:70-112): blocks with a fixed pose (index < 0) are skipped, duplicates are summed.
@@ -167,6 +234,31 @@ __device__ bool cholesky_solve(Mat L, int D, double *x, double *col, int *fail) 
   return true;
 }
 
+// dx = -x (f32; zeros on failure), ||dx||_2 taken on the f32 values like the reference's
+// linalg_norm (:1218), retraction of the free poses, iteration bookkeeping.  One CTA.
+__device__ inline void finish_update(bool ok, const double *x, double *scratch, int D, int N, float *Twc,
+                                     float *dx, float delta_thresh, State *state) {
+  const int tid = threadIdx.x;
+  double part = 0.0;
+  for (int i = tid; i < D; i += blockDim.x) {
+    const float v = ok ? -(float)x[i] : 0.0f;
+    dx[i] = v;
+    part += (double)v * (double)v;
+  }
+  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  __syncthreads();
+  if ((tid & 31) == 0) scratch[tid >> 5] = part;  // scratch: >= 32 doubles
+  __syncthreads();
+  for (int k = NUM_FIX + tid; k < N; k += blockDim.x) retract_pose(Twc + 8 * k, dx + 7 * (k - NUM_FIX));
+  if (tid == 0) {
+    double s = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); w++) s += scratch[w];
+    state->iters += 1;
+    if (!ok) state->chol_fail += 1;
+    if ((float)sqrt(s) < delta_thresh) state->done = 1;
+  }
+}
+
 constexpr int SOLVE_THREADS = 1024;
 constexpr int PACKED_MAX_D = 217;  // 217*218/2*8 = 189 KB of packed lower triangle in smem
 
@@ -179,7 +271,6 @@ solve_retract_kernel(float *__restrict__ Twc, double *__restrict__ A, const doub
   extern __shared__ double sm[];
   double *x = sm, *col = sm + Dp;  // Dp = max(D, 32): col doubles as the cross-warp scratch
   __shared__ int fail;
-  __shared__ double nrm2;
   const int tid = threadIdx.x;
   for (int i = tid; i < D; i += blockDim.x) x[i] = rhs[i];
   bool ok;
@@ -194,33 +285,55 @@ solve_retract_kernel(float *__restrict__ Twc, double *__restrict__ A, const doub
     __syncthreads();
     ok = cholesky_solve(L, D, x, col, &fail);
   }
-  // dx = -x (f32), zeros on failure;  ||dx||_2 in the reference is taken on the f32 tensor
-  if (tid == 0) nrm2 = 0.0;
+  finish_update(ok, x, col, D, N, Twc, dx, delta_thresh, state);
+}
+
+// ---- fused tail for small problems (D <= SMALL_MAX_D): executed by the LAST stage-1 CTA of an
+// iteration (ticket counter), so a whole GN iteration is ONE kernel launch. ---------------------
+constexpr int SMALL_MAX_D = 63;   // N <= 10 poses
+constexpr int SMALL_MAX_E = 96;
+
+__device__ inline void small_tail(float *Twc, const int64_t *ii_row, const int64_t *jj_row,
+                                  const double *partials, int S, int E, int N, float delta_thresh, float *dx,
+                                  double *edge_blocks, State *state) {
+  __shared__ double sc[BUILD_THREADS / 32][FIN_SCRATCH];
+  __shared__ double Ap[SMALL_MAX_D * (SMALL_MAX_D + 1) / 2];
+  __shared__ double xs[64], cols[64];
+  __shared__ int fail;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int D = 7 * (N - NUM_FIX);
+  for (int e = warp; e < E; e += BUILD_THREADS / 32) finalize_edge(Twc, ii_row, partials, S, e, edge_blocks + (size_t)e * 56, sc[warp], lane);
   __syncthreads();
-  double part = 0.0;
-  for (int i = tid; i < D; i += blockDim.x) {
-    const float v = ok ? -(float)x[i] : 0.0f;
-    dx[i] = v;
-    part += (double)v * (double)v;
-  }
-  for (int o = 16; o > 0; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
-  __syncthreads();
-  // deterministic cross-warp sum
-  double *wsum = col;
-  if ((tid & 31) == 0) wsum[tid >> 5] = part;
-  __syncthreads();
-  if (tid == 0) {
+  PackedLower L{Ap};
+  for (int t = tid; t < D * D; t += BUILD_THREADS) {
+    const int r = t / D, c = t % D;
+    if (c > r) continue;
+    const int br = r / 7, kr = r % 7, bc = c / 7, kc = c % 7;
     double s = 0.0;
-    for (int w = 0; w < (int)(blockDim.x >> 5); w++) s += wsum[w];
-    nrm2 = s;
+    for (int e = 0; e < E; e++) {
+      const int i = (int)ii_row[e] - NUM_FIX, j = (int)jj_row[e] - NUM_FIX;
+      const double v = edge_blocks[(size_t)e * 56 + kr * 7 + kc];
+      if (i == br && i == bc) s += v;
+      if (i == br && j == bc) s -= v;
+      if (j == br && j == bc) s += v;
+      if (j == br && i == bc) s -= v;
+    }
+    L.at(r, c) = s;
+  }
+  for (int r = tid; r < D; r += BUILD_THREADS) {
+    const int br = r / 7, kr = r % 7;
+    double s = 0.0;
+    for (int e = 0; e < E; e++) {
+      const int i = (int)ii_row[e] - NUM_FIX, j = (int)jj_row[e] - NUM_FIX;
+      const double v = edge_blocks[(size_t)e * 56 + 49 + kr];
+      if (i == br) s -= v;
+      if (j == br) s += v;
+    }
+    xs[r] = s;
   }
   __syncthreads();
-  for (int k = NUM_FIX + tid; k < N; k += blockDim.x) retract_pose(Twc + 8 * k, dx + 7 * (k - NUM_FIX));
-  if (tid == 0) {
-    state->iters += 1;
-    if (!ok) state->chol_fail += 1;
-    if ((float)sqrt(nrm2) < delta_thresh) state->done = 1;
-  }
+  const bool ok = cholesky_solve(L, D, xs, cols, &fail);
+  finish_update(ok, xs, cols, D, N, Twc, dx, delta_thresh, state);
 }
 
 }  // namespace b200gn

@@ -34,7 +34,9 @@ def _load():
     vp, i, f, sz = ctypes.c_void_p, ctypes.c_int, ctypes.c_float, ctypes.c_size_t
     P = ctypes.POINTER(GNParams)
     lib.b200slam_version.restype = i
-    lib.b200slam_iter_proj.argtypes = [vp] * 5 + [i] * 5 + [f, f, vp]
+    lib.b200slam_iter_proj.argtypes = [vp] * 5 + [i] * 5 + [f, f, vp, sz, vp]
+    lib.b200slam_iter_proj_workspace_bytes.argtypes = [i, i, i]
+    lib.b200slam_iter_proj_workspace_bytes.restype = sz
     lib.b200slam_refine_matches_f16.argtypes = [vp] * 4 + [i] * 7 + [vp]
     lib.b200slam_refine_matches_f32.argtypes = [vp] * 4 + [i] * 7 + [vp]
     lib.b200slam_gn_workspace_bytes.argtypes = [i, i, i]
@@ -90,9 +92,11 @@ def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, co
     with torch.cuda.device(p_init.device):
         p_new = torch.empty((b, n, 2), dtype=torch.float32, device=p_init.device)
         conv = torch.empty((b, n), dtype=torch.bool, device=p_init.device)
+        nbytes = _lib.b200slam_iter_proj_workspace_bytes(b, h, w)
+        ws = torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=p_init.device)
         _check(_lib.b200slam_iter_proj(
             *ptrs, p_new.data_ptr(), conv.data_ptr(), b, h, w, n, int(max_iter), float(lambda_init),
-            float(cost_thresh), _stream(p_init)), "iter_proj")
+            float(cost_thresh), ws.data_ptr(), nbytes, _stream(p_init)), "iter_proj")
     return [p_new, conv]
 
 
