@@ -44,10 +44,24 @@ constexpr int FIN_SCRATCH = 36 + 49 + 49;  // doubles of shared scratch per warp
 __device__ inline void finalize_edge(const float *Twc, const int64_t *ii_row, const double *partials, int S,
                                      int e, double *out, double *sc, int lane) {
   double *acc = sc, *M = sc + 36, *T = sc + 36 + 49;
-  for (int l = lane; l < NACC; l += 32) {
-    double s = 0.0;
-    for (int k = 0; k < S; k++) s += partials[((size_t)e * S + k) * NACC + l];
-    acc[l] = s;
+  // lane L owns splits L, L+32, ... (all 35 sums independent -> loads pipeline), then a fixed
+  // xor-shuffle tree combines the lanes: deterministic, no serial chain over S.
+  {
+    double s[NACC];
+#pragma unroll
+    for (int l = 0; l < NACC; l++) s[l] = 0.0;
+    for (int k = lane; k < S; k += 32) {
+      const double *p = partials + ((size_t)e * S + k) * NACC;
+#pragma unroll
+      for (int l = 0; l < NACC; l++) s[l] += p[l];
+    }
+#pragma unroll
+    for (int l = 0; l < NACC; l++) {
+      double v = s[l];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) acc[l] = v;
+    }
   }
   if (lane == 0) adj_inv_matrix(Twc + 8 * (int)ii_row[e], M);
   __syncwarp();

@@ -167,9 +167,10 @@ extern "C" int b200slam_iter_proj(const float *rays_img, const float *pts_3d_nor
                                   int h, int w, int n, int max_iter, float lambda_init,
                                   float cost_thresh, void *workspace, size_t workspace_bytes,
                                   void *stream) {
+  if (b < 0 || n < 0) return B200SLAM_EINVAL;
+  if (b == 0 || n == 0) return B200SLAM_OK;  // empty inputs: nothing to do (pointers may be null)
   if (!rays_img || !pts_3d_norm || !p_init || !p_new || !converged) return B200SLAM_EINVAL;
-  if (b < 0 || n < 0 || h < 3 || w < 3 || (long long)h * w * 9 > 0x7fffffffLL) return B200SLAM_EINVAL;
-  if (b == 0 || n == 0) return B200SLAM_OK;
+  if (h < 3 || w < 3 || (long long)h * w * 9 > 0x7fffffffLL) return B200SLAM_EINVAL;
   if (!workspace || workspace_bytes < b200slam_iter_proj_workspace_bytes(b, h, w)) return B200SLAM_EWORKSPACE;
   cudaStream_t st = (cudaStream_t)stream;
   float *planes = (float *)workspace;

@@ -163,9 +163,10 @@ refine_f32_kernel(const float *__restrict__ D11, const float *__restrict__ D21,
 extern "C" int b200slam_refine_matches_f16(const void *D11, const void *D21, const int64_t *p1,
                                            int64_t *p1_new, int b, int h, int w, int n, int fdim,
                                            int radius, int dilation_max, void *stream) {
-  if (!D11 || !D21 || !p1 || !p1_new) return B200SLAM_EINVAL;
-  if (b < 0 || n < 0 || h < 1 || w < 1 || fdim < 0 || radius < 0) return B200SLAM_EINVAL;
+  if (b < 0 || n < 0) return B200SLAM_EINVAL;
   if (b == 0 || n == 0) return B200SLAM_OK;
+  if (!D11 || !D21 || !p1 || !p1_new) return B200SLAM_EINVAL;
+  if (h < 1 || w < 1 || fdim < 0 || radius < 0) return B200SLAM_EINVAL;
   dim3 grid((n + RF_THREADS - 1) / RF_THREADS, b);
   cudaStream_t st = (cudaStream_t)stream;
   const __half *a = (const __half *)D11, *q = (const __half *)D21;
@@ -185,9 +186,10 @@ extern "C" int b200slam_refine_matches_f16(const void *D11, const void *D21, con
 extern "C" int b200slam_refine_matches_f32(const float *D11, const float *D21, const int64_t *p1,
                                            int64_t *p1_new, int b, int h, int w, int n, int fdim,
                                            int radius, int dilation_max, void *stream) {
-  if (!D11 || !D21 || !p1 || !p1_new) return B200SLAM_EINVAL;
-  if (b < 0 || n < 0 || h < 1 || w < 1 || fdim < 0 || radius < 0) return B200SLAM_EINVAL;
+  if (b < 0 || n < 0) return B200SLAM_EINVAL;
   if (b == 0 || n == 0) return B200SLAM_OK;
+  if (!D11 || !D21 || !p1 || !p1_new) return B200SLAM_EINVAL;
+  if (h < 1 || w < 1 || fdim < 0 || radius < 0) return B200SLAM_EINVAL;
   dim3 grid((n + RF_THREADS - 1) / RF_THREADS, b);
   refine_f32_kernel<<<grid, RF_THREADS, 0, (cudaStream_t)stream>>>(D11, D21, p1, p1_new, h, w, n,
                                                                    fdim, radius, dilation_max);

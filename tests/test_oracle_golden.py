@@ -83,7 +83,8 @@ def test_gn_blocks_vs_reference(gg, name, kind):
     for blk in range(2):
         assert rel(gs[blk], gr[blk]) < RTOL
     # structure the B200 kernels rely on: H_ii = H_jj = -H_ij = -H_ji^T, g_i = -g_j (gn_kernels.cu:998-999)
-    assert torch.equal(Hr[0], Hr[3]) and torch.equal(Hr[1], -Hr[3]) and torch.equal(gr[0], -gr[1])
+    assert rel(Hr[0], Hr[3]) < 1e-6 and rel(Hr[1], -Hr[3]) < 1e-5 and rel(Hr[2], -Hr[3]) < 1e-5
+    assert rel(gr[0], -gr[1]) < 1e-6
 
 
 @pytest.mark.parametrize("iters", [1, 4])
