@@ -113,6 +113,21 @@ int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, const float
                           const float *Q, int N, int E, int n, int max_iter, float delta_thresh,
                           float *dx, void *workspace, size_t workspace_bytes, void *stream);
 
+/* Keyframe ids -> rows of Twc/Xs/Cs: rows[0..E) for ii, rows[E..2E) for jj; row = rank of the id
+ * among the sorted distinct ids of cat(ii, jj).  Replaces get_unique_kf_idx / create_inds
+ * (torch::_unique + searchsorted, gn_kernels.cu:160-169).  scratch: 2*E bytes. */
+int b200slam_edge_rows(const int64_t *ii, const int64_t *jj, int E, int64_t *rows, void *scratch,
+                       size_t scratch_bytes, void *stream);
+
+/* Same as b200slam_gauss_newton but takes the KEYFRAME IDS the reference's pybind functions take
+ * (gn.cpp:28-82) and derives the rows on the device; nothing in the call synchronises the host
+ * (except the 36-byte read of K for the calib model). */
+int b200slam_gauss_newton_ids(const b200slam_gn_params *prm, float *Twc, const float *Xs,
+                              const float *Cs, const float *K, const int64_t *ii, const int64_t *jj,
+                              const int64_t *idx, const uint8_t *valid, const float *Q, int N, int E,
+                              int n, int max_iter, float delta_thresh, float *dx, void *workspace,
+                              size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

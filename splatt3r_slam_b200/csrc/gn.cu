@@ -4,6 +4,7 @@
 // reference (gn_kernels.cu:56-158, :414-452, :724-810, :1139-1227, :1545-1637).
 // The whole max_iter loop is enqueued on one stream with NO host round trip per iteration
 // (the reference does D2H -> Eigen SimplicialLLT on the CPU -> H2D -> .item() each iteration).
+#include <cuda/atomic>
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
@@ -19,20 +20,27 @@ struct State {  // head of the workspace
   int done;       // set when ||dx|| < delta_thresh: later launches are no-ops
   int chol_fail;  // number of failed factorisations (dx = 0)
   unsigned ticket;  // arrival counter of the fused small-problem path (reset by the last CTA)
+  unsigned long long t[4];  // %globaltimer stamps of the last fused tail: start, finalized, solved, end
 };
+__device__ __forceinline__ unsigned long long gtimer() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+  return t;
+}
 constexpr size_t STATE_BYTES = 256;
 constexpr int MAX_SPLITS = 296;
 
 __host__ __device__ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Layout {
-  size_t partials, edge_blocks, A, rhs, total;
+  size_t partials, edge_blocks, A, rhs, rows, first, total;
   int S;
 };
 
 inline int choose_splits(int E, int n) {
-  // aim for >= 2 CTAs per SM (148 SMs) but never fewer than 1024 points per CTA
-  int S = (2 * 148 + E - 1) / E;
+  // one CTA per SM (148 SMs; the build kernel's ~140 registers x 256 threads allow 1 CTA/SM), so
+  // small graphs run as a single wave; never fewer than 1024 points per CTA
+  int S = 148 / E;
   const int maxS = (n + 1023) / 1024;
   if (S > maxS) S = maxS;
   if (S > MAX_SPLITS) S = MAX_SPLITS;
@@ -49,6 +57,8 @@ inline Layout make_layout(int N, int E, int n) {
   L.edge_blocks = off; off = align256(off + (size_t)E * 56 * sizeof(double));
   L.A = off; off = align256(off + D * D * sizeof(double));
   L.rhs = off; off = align256(off + D * sizeof(double));
+  L.rows = off; off = align256(off + (size_t)2 * E * sizeof(int64_t));
+  L.first = off; off = align256(off + (size_t)2 * E);
   L.total = off;
   return L;
 }
@@ -68,6 +78,9 @@ build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__
              const float *__restrict__ Q, int n, int e0, BuildConsts C, double *partials, State *state,
              int N, int E, float delta_thresh, float *dx, double *edge_blocks) {
   if (state->done) return;
+  if (KIND == B200SLAM_GN_CALIB) {  // gn_kernels.cu:1273-1278
+    C.fx = __ldg(C.Kptr + 0); C.fy = __ldg(C.Kptr + 4); C.cx = __ldg(C.Kptr + 2); C.cy = __ldg(C.Kptr + 5);
+  }
   const int e = e0 + blockIdx.y;
   const int S = gridDim.x, s = blockIdx.x;
   const int ix = (int)ii_row[e], jx = (int)jj_row[e];
@@ -146,16 +159,42 @@ build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__
   }
   if (FUSED) {
     // last-arriving CTA finishes the iteration: finalize + assemble + solve + retract
+    // (release: this CTA's partials; acquire: everyone else's) through one acq_rel RMW
     __shared__ bool is_last;
-    __threadfence();
     __syncthreads();
-    if (threadIdx.x == 0) is_last = atomicAdd(&state->ticket, 1u) == gridDim.x * gridDim.y - 1;
+    if (threadIdx.x == 0) {
+      cuda::atomic_ref<unsigned, cuda::thread_scope_device> ticket(state->ticket);
+      is_last = ticket.fetch_add(1u, cuda::memory_order_acq_rel) == gridDim.x * gridDim.y - 1;
+    }
     __syncthreads();
     if (!is_last) return;
-    __threadfence();
-    if (threadIdx.x == 0) state->ticket = 0;
+    if (threadIdx.x == 0) { state->ticket = 0; state->t[0] = gtimer(); }
     small_tail(Twc, ii_row, jj_row, partials, S, E, N, delta_thresh, dx, edge_blocks, state);
   }
+}
+
+// ---- keyframe ids -> rows (replaces torch::_unique + searchsorted, gn_kernels.cu:160-169) --------
+// row(x) = number of distinct ids smaller than x among cat(ii, jj).
+__device__ __forceinline__ int64_t id_at(const int64_t *ii, const int64_t *jj, int E, int p) {
+  return p < E ? ii[p] : jj[p - E];
+}
+__global__ void first_occurrence_kernel(const int64_t *__restrict__ ii, const int64_t *__restrict__ jj, int E,
+                                        uint8_t *__restrict__ first) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= 2 * E) return;
+  const int64_t x = id_at(ii, jj, E, p);
+  bool f = true;
+  for (int q = 0; q < p && f; q++) f = id_at(ii, jj, E, q) != x;
+  first[p] = f ? 1 : 0;
+}
+__global__ void rank_kernel(const int64_t *__restrict__ ii, const int64_t *__restrict__ jj, int E,
+                            const uint8_t *__restrict__ first, int64_t *__restrict__ rows) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= 2 * E) return;
+  const int64_t x = id_at(ii, jj, E, p);
+  int r = 0;
+  for (int q = 0; q < 2 * E; q++) r += (first[q] && id_at(ii, jj, E, q) < x) ? 1 : 0;
+  rows[p] = r;  // rows[0..E) = ii_row, rows[E..2E) = jj_row
 }
 
 // ---- stage 2 (large problems): one warp per edge -----------------------------------------------

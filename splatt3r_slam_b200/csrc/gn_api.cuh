@@ -3,13 +3,14 @@
 
 namespace b200gn {
 
-inline BuildConsts make_consts(const b200slam_gn_params *p, const float *Kdev_host_copy) {
+inline BuildConsts make_consts(const b200slam_gn_params *p, const float *K) {
   BuildConsts C;
   C.sa_inv = 1.0f / p->sigma_a;
   C.sb_inv = 1.0f / p->sigma_b;
   C.C_thresh = p->C_thresh;
   C.Q_thresh = p->Q_thresh;
-  C.fx = Kdev_host_copy[0]; C.fy = Kdev_host_copy[4]; C.cx = Kdev_host_copy[2]; C.cy = Kdev_host_copy[5];
+  C.fx = C.fy = C.cx = C.cy = 0.0f;
+  C.Kptr = K;
   C.z_eps = p->z_eps;
   C.ulo = (float)p->pixel_border;
   C.uhi = (float)(p->width - 1 - p->pixel_border);
@@ -19,19 +20,8 @@ inline BuildConsts make_consts(const b200slam_gn_params *p, const float *Kdev_ho
   return C;
 }
 
-// K lives on the device (it is a torch CUDA tensor in the reference).  The 4 intrinsics are
-// fetched once per call with a small D2H copy; callers that want a fully asynchronous call
-// can pass K == NULL for the rays/points models.
-inline int fetch_K(const b200slam_gn_params *p, const float *K, float *Kh, cudaStream_t st) {
-  for (int i = 0; i < 9; i++) Kh[i] = 0.0f;
-  if (p->kind == B200SLAM_GN_CALIB) {
-    if (!K) return B200SLAM_EINVAL;
-    cudaError_t err = cudaMemcpyAsync(Kh, K, 9 * sizeof(float), cudaMemcpyDeviceToHost, st);
-    if (err != cudaSuccess) return (int)err;
-    err = cudaStreamSynchronize(st);
-    if (err != cudaSuccess) return (int)err;
-  }
-  return 0;
+inline int check_K(const b200slam_gn_params *p, const float *K) {
+  return (p->kind == B200SLAM_GN_CALIB && !K) ? B200SLAM_EINVAL : 0;
 }
 
 // Tail arguments of the fused small-problem path (ignored when fused == false).
@@ -173,10 +163,9 @@ extern "C" int b200slam_gn_edge_blocks(const b200slam_gn_params *prm, const floa
   const Layout L = make_layout(N, E, n);
   if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
   cudaStream_t st = (cudaStream_t)stream;
-  float Kh[9];
-  int rc = fetch_K(prm, K, Kh, st);
+  int rc = check_K(prm, K);
   if (rc) return rc;
-  const BuildConsts C = make_consts(prm, Kh);
+  const BuildConsts C = make_consts(prm, K);
   return launch_edge_blocks(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, E, n, e0, Ecount,
                             edge_blocks, (char *)workspace, L, st);
 }
@@ -207,6 +196,19 @@ extern "C" int b200slam_gn_solve_retract(float *Twc, const int64_t *ii_row, cons
                       (cudaStream_t)stream);
 }
 
+extern "C" int b200slam_edge_rows(const int64_t *ii, const int64_t *jj, int E, int64_t *rows,
+                                  void *scratch, size_t scratch_bytes, void *stream) {
+  if (E < 0) return B200SLAM_EINVAL;
+  if (E == 0) return B200SLAM_OK;
+  if (!ii || !jj || !rows || !scratch) return B200SLAM_EINVAL;
+  if (scratch_bytes < (size_t)2 * E) return B200SLAM_EWORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int blocks = (2 * E + 127) / 128;
+  first_occurrence_kernel<<<blocks, 128, 0, st>>>(ii, jj, E, (uint8_t *)scratch);
+  rank_kernel<<<blocks, 128, 0, st>>>(ii, jj, E, (const uint8_t *)scratch, rows);
+  return (int)cudaGetLastError();
+}
+
 extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, const float *Xs,
                                      const float *Cs, const float *K, const int64_t *ii_row,
                                      const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
@@ -218,10 +220,9 @@ extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, 
   if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
   cudaStream_t st = (cudaStream_t)stream;
   char *ws = (char *)workspace;
-  float Kh[9];
-  int rc = fetch_K(prm, K, Kh, st);
+  int rc = check_K(prm, K);
   if (rc) return rc;
-  const BuildConsts C = make_consts(prm, Kh);
+  const BuildConsts C = make_consts(prm, K);
   rc = (int)cudaMemsetAsync(ws, 0, STATE_BYTES, st);
   if (rc) return rc;
   double *eb = reinterpret_cast<double *>(ws + L.edge_blocks);
@@ -240,4 +241,21 @@ extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, 
     if (rc) return rc;
   }
   return 0;
+}
+
+extern "C" int b200slam_gauss_newton_ids(const b200slam_gn_params *prm, float *Twc, const float *Xs,
+                                         const float *Cs, const float *K, const int64_t *ii,
+                                         const int64_t *jj, const int64_t *idx, const uint8_t *valid,
+                                         const float *Q, int N, int E, int n, int max_iter,
+                                         float delta_thresh, float *dx, void *workspace,
+                                         size_t workspace_bytes, void *stream) {
+  if (!ii || !jj || !workspace || E < 0 || N < 1) return B200SLAM_EINVAL;
+  const Layout L = make_layout(N, E, n);
+  if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
+  char *ws = (char *)workspace;
+  int64_t *rows = reinterpret_cast<int64_t *>(ws + L.rows);
+  int rc = b200slam_edge_rows(ii, jj, E, rows, ws + L.first, (size_t)2 * E, stream);
+  if (rc) return rc;
+  return b200slam_gauss_newton(prm, Twc, Xs, Cs, K, rows, rows + E, idx, valid, Q, N, E, n, max_iter,
+                               delta_thresh, dx, workspace, workspace_bytes, stream);
 }

@@ -85,6 +85,7 @@ struct BuildConsts {
   float sa_inv, sb_inv, C_thresh, Q_thresh;
   float fx, fy, cx, cy, z_eps, ulo, uhi, vlo, vhi;
   int width;
+  const float *Kptr;  // device (3,3) intrinsics, read by the calib kernel itself (no host sync)
 };
 
 // One point.  Xi/ci = matched point of keyframe i, Xj/cj = point k of keyframe j.

@@ -53,7 +53,7 @@ __device__ inline void finalize_edge(const float *Twc, const int64_t *ii_row, co
     for (int k = lane; k < S; k += 32) {
       const double *p = partials + ((size_t)e * S + k) * NACC;
 #pragma unroll
-      for (int l = 0; l < NACC; l++) s[l] += p[l];
+      for (int l = 0; l < NACC; l++) s[l] += __ldcg(p + l);
     }
 #pragma unroll
     for (int l = 0; l < NACC; l++) {
@@ -201,19 +201,21 @@ struct FullLower {
 // Right-looking Cholesky + two triangular solves by ONE CTA.  Returns false when a pivot is
 // not positive (the reference's "solver.info() != Success" => dx = 0, :141-149).
 // x (length D, shared) holds the rhs on entry and the solution on exit; col is scratch (D).
-template <class Mat>
+// WARP = true: executed by the 32 threads of warp 0 only (D <= 32), __syncwarp instead of barriers.
+template <class Mat, bool WARP = false>
 __device__ bool cholesky_solve(Mat L, int D, double *x, double *col, int *fail) {
-  const int tid = threadIdx.x, T = blockDim.x;
+#define CHOL_SYNC() do { if (WARP) __syncwarp(); else __syncthreads(); } while (0)
+  const int tid = threadIdx.x, T = WARP ? 32 : blockDim.x;
   const int lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
   if (tid == 0) *fail = 0;
-  __syncthreads();
+  CHOL_SYNC();
   for (int j = 0; j < D; j++) {
     if (tid == 0) {
       const double d = L.at(j, j);
       if (!(d > 0.0)) *fail = 1;
       else L.at(j, j) = sqrt(d);
     }
-    __syncthreads();
+    CHOL_SYNC();
     if (*fail) return false;
     const double dinv = 1.0 / L.at(j, j);
     for (int i = j + 1 + tid; i < D; i += T) {
@@ -221,31 +223,32 @@ __device__ bool cholesky_solve(Mat L, int D, double *x, double *col, int *fail) 
       L.at(i, j) = v;
       col[i] = v;
     }
-    __syncthreads();
+    CHOL_SYNC();
     // trailing update: row i (one warp per row), k over lanes
     for (int i = j + 1 + warp; i < D; i += nwarp) {
       const double ci = col[i];
       for (int k = j + 1 + lane; k <= i; k += 32) L.at(i, k) -= ci * col[k];
     }
-    __syncthreads();
+    CHOL_SYNC();
   }
   // forward: L y = b
   for (int j = 0; j < D; j++) {
     if (tid == 0) x[j] = x[j] / L.at(j, j);
-    __syncthreads();
+    CHOL_SYNC();
     const double yj = x[j];
     for (int i = j + 1 + tid; i < D; i += T) x[i] -= L.at(i, j) * yj;
-    __syncthreads();
+    CHOL_SYNC();
   }
   // backward: L^T x = y
   for (int j = D - 1; j >= 0; j--) {
     if (tid == 0) x[j] = x[j] / L.at(j, j);
-    __syncthreads();
+    CHOL_SYNC();
     const double xj = x[j];
     for (int i = tid; i < j; i += T) x[i] -= L.at(j, i) * xj;
-    __syncthreads();
+    CHOL_SYNC();
   }
   return true;
+#undef CHOL_SYNC
 }
 
 // dx = -x (f32; zeros on failure), ||dx||_2 taken on the f32 values like the reference's
@@ -318,6 +321,7 @@ __device__ inline void small_tail(float *Twc, const int64_t *ii_row, const int64
   const int D = 7 * (N - NUM_FIX);
   for (int e = warp; e < E; e += BUILD_THREADS / 32) finalize_edge(Twc, ii_row, partials, S, e, edge_blocks + (size_t)e * 56, sc[warp], lane);
   __syncthreads();
+  if (tid == 0) state->t[1] = gtimer();
   PackedLower L{Ap};
   for (int t = tid; t < D * D; t += BUILD_THREADS) {
     const int r = t / D, c = t % D;
@@ -346,8 +350,17 @@ __device__ inline void small_tail(float *Twc, const int64_t *ii_row, const int64
     xs[r] = s;
   }
   __syncthreads();
-  const bool ok = cholesky_solve(L, D, xs, cols, &fail);
+  bool ok;
+  if (D <= 32) {  // tiny system (tracker: 7 unknowns): one warp, no block barriers
+    if (warp == 0) cholesky_solve<PackedLower, true>(L, D, xs, cols, &fail);
+    __syncthreads();
+    ok = fail == 0;
+  } else {
+    ok = cholesky_solve(L, D, xs, cols, &fail);
+  }
+  if (tid == 0) state->t[2] = gtimer();
   finish_update(ok, xs, cols, D, N, Twc, dx, delta_thresh, state);
+  if (tid == 0) state->t[3] = gtimer();
 }
 
 }  // namespace b200gn

@@ -47,8 +47,11 @@ def _load():
     lib.b200slam_gn_reset.argtypes = [vp, sz, vp]
     lib.b200slam_gn_status.argtypes = [vp, ctypes.POINTER(i), ctypes.POINTER(i), ctypes.POINTER(i), vp]
     lib.b200slam_gauss_newton.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
+    lib.b200slam_gauss_newton_ids.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
+    lib.b200slam_edge_rows.argtypes = [vp, vp, i, vp, vp, sz, vp]
     for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "gn_build_blocks",
-                 "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gauss_newton"):
+                 "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gauss_newton",
+                 "gauss_newton_ids", "edge_rows"):
         getattr(lib, "b200slam_" + name).restype = i
     return lib
 
@@ -81,6 +84,22 @@ def _stream(t):
     return torch.cuda.current_stream(t.device).cuda_stream
 
 
+class _NoGuard:
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        return False
+
+
+_NOGUARD = _NoGuard()
+
+
+def _guard(t):
+    """Device guard only when needed (torch.cuda.device costs ~10 us per call otherwise)."""
+    return _NOGUARD if t.device.index == torch.cuda.current_device() else torch.cuda.device(t.device)
+
+
 def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, cost_thresh):
     _contig(rays_img_with_grad=rays_img_with_grad, pts_3d_norm=pts_3d_norm, p_init=p_init)
     b, h, w, c = rays_img_with_grad.shape
@@ -89,7 +108,7 @@ def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, co
     n = p_init.shape[1]
     ptrs = (_cuda(rays_img_with_grad, torch.float32, "rays_img_with_grad"),
             _cuda(pts_3d_norm, torch.float32, "pts_3d_norm"), _cuda(p_init, torch.float32, "p_init"))
-    with torch.cuda.device(p_init.device):
+    with _guard(p_init):
         p_new = torch.empty((b, n, 2), dtype=torch.float32, device=p_init.device)
         conv = torch.empty((b, n), dtype=torch.bool, device=p_init.device)
         nbytes = _lib.b200slam_iter_proj_workspace_bytes(b, h, w)
@@ -111,7 +130,7 @@ def refine_matches(D11, D21, p1, radius, dilation_max):
     else:
         raise RuntimeError(f"refine_matches: unsupported descriptor dtype {D11.dtype}")
     ptrs = (_cuda(D11, D11.dtype, "D11"), _cuda(D21, D11.dtype, "D21"), _cuda(p1, torch.int64, "p1"))
-    with torch.cuda.device(p1.device):
+    with _guard(p1):
         p1_new = torch.empty((b, n, 2), dtype=torch.int64, device=p1.device)
         _check(fn(*ptrs, p1_new.data_ptr(), b, h, w, n, fdim, int(radius), int(dilation_max), _stream(p1)),
                "refine_matches")
@@ -120,8 +139,17 @@ def refine_matches(D11, D21, p1, radius, dilation_max):
 
 def edge_rows(ii, jj):
     """Keyframe ids -> rows of Twc/Xs/Cs: dense rank among the sorted unique ids
-    (reference: torch::_unique + searchsorted, gn_kernels.cu:160-169).  No host sync."""
+    (reference: torch::_unique + searchsorted, gn_kernels.cu:160-169).  No host sync.
+    CUDA tensors go through the library's kernel; CPU tensors (tests, gloo ranks) through torch."""
     E = ii.numel()
+    if ii.is_cuda and E > 0:
+        rows = torch.empty(2 * E, dtype=torch.int64, device=ii.device)
+        scratch = torch.empty(2 * E, dtype=torch.uint8, device=ii.device)
+        with _guard(ii):
+            _check(_lib.b200slam_edge_rows(_cuda(ii.contiguous(), torch.int64, "ii"),
+                                           _cuda(jj.contiguous(), torch.int64, "jj"), E, rows.data_ptr(),
+                                           scratch.data_ptr(), 2 * E, _stream(ii)), "edge_rows")
+        return rows[:E], rows[E:]
     s, order = torch.sort(torch.cat([ii, jj]))
     rank_sorted = torch.cumsum(torch.cat([s.new_zeros(1), (s[1:] != s[:-1]).to(s.dtype)]), 0)
     rows = torch.empty_like(rank_sorted)
@@ -154,19 +182,17 @@ def _gauss_newton(prm, Twc, Xs, Cs, K, ii, jj, idx, valid, Q, max_iter, delta_th
         _contig(K=K)
     N, n = Xs.shape[0], Xs.shape[1]
     E = ii.shape[0]
-    _cuda(Twc, torch.float32, "Twc")
-    if max_iter <= 0 or N < 2 or E == 0:
-        return [torch.zeros((max(N - 1, 0), 7), dtype=torch.float32, device=Twc.device)]
-    with torch.cuda.device(Twc.device):
-        _cuda(ii, torch.int64, "ii"), _cuda(jj, torch.int64, "jj")
-        ii_row, jj_row = edge_rows(ii, jj)
-        dx = torch.zeros((N - 1, 7), dtype=torch.float32, device=Twc.device)
+    ptrs = _gn_ptrs(Twc, Xs, Cs, K, ii, jj, idx, valid, Q)
+    _cuda(ii, torch.int64, "ii"), _cuda(jj, torch.int64, "jj")
+    with _guard(Twc):
+        dx = torch.zeros((max(N - 1, 0), 7), dtype=torch.float32, device=Twc.device)
+        if max_iter <= 0 or N < 2 or E == 0:
+            return [dx]
         nbytes = _lib.b200slam_gn_workspace_bytes(N, E, n)
         ws = _workspace(Twc.device, nbytes)
-        _check(_lib.b200slam_gauss_newton(
-            ctypes.byref(prm), *_gn_ptrs(Twc, Xs, Cs, K, ii_row, jj_row, idx, valid, Q), N, E, n,
-            int(max_iter), float(delta_thresh), dx.data_ptr(), ws.data_ptr(), nbytes, _stream(Twc)),
-            "gauss_newton")
+        _check(_lib.b200slam_gauss_newton_ids(
+            ctypes.byref(prm), *ptrs, N, E, n, int(max_iter), float(delta_thresh), dx.data_ptr(),
+            ws.data_ptr(), nbytes, _stream(Twc)), "gauss_newton")
     return [dx]
 
 
@@ -197,7 +223,7 @@ def make_params(kind, sigma_a, sigma_b, C_thresh, Q_thresh, height=0, width=0, p
 def gn_build_blocks(prm, Twc, Xs, Cs, K, ii, jj, idx, valid, Q):
     """One Hessian build in the reference's private layout: Hs (4,E,7,7), gs (2,E,7) fp32."""
     N, n, E = Xs.shape[0], Xs.shape[1], ii.shape[0]
-    with torch.cuda.device(Twc.device):
+    with _guard(Twc):
         ii_row, jj_row = edge_rows(ii, jj)
         Hs = torch.zeros((4, E, 7, 7), dtype=torch.float32, device=Twc.device)
         gs = torch.zeros((2, E, 7), dtype=torch.float32, device=Twc.device)

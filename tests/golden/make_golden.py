@@ -40,7 +40,7 @@ def main(out_dir):
 
     # ---- matching: b=2 pairs of 64x48 ------------------------------------------------------
     h, w = 48, 64
-    X11, X21, D11, D21 = [t.to(dev) for t in synthetic.make_pair(seed=11, h=h, w=w, fdim=24, b=2)]
+    X11, X21, D11, D21 = [t.to(dev) for t in synthetic.make_pair(seed=11, h=h, w=w, fdim=24, b=2, noise=0.005)]
     rays, pts, p_init = matching.prep_for_iter_proj(X11, X21, None)
     # second batch row starts from a shifted, partly out-of-range initial guess (tests the clamp)
     p_init[1] = p_init[1] + torch.tensor([7.5, -3.25], device=dev)
@@ -60,7 +60,7 @@ def main(out_dir):
         p1_refined=p1_ref.cpu().numpy(), p1_refined_f32=p1_ref_f32.cpu().numpy())
 
     # ---- GN: N=3 keyframes, 3 undirected = 6 directed edges, 64x48 -------------------------
-    g = synthetic.make_graph(seed=5, N=3, E_undirected=3, h=h, w=w)
+    g = synthetic.make_graph(seed=5, N=3, E_undirected=3, h=h, w=w, noise=0.005)
     G = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in g.items()}
     c = GN_CFG
     out = {k: g[k].numpy() for k in ("Twc", "Xs", "Cs", "K", "ii", "jj", "idx_ii2jj", "valid_match", "Q")}
