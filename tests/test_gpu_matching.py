@@ -133,3 +133,25 @@ def test_error_convention(backend):
         backend.refine_matches(torch.zeros(1, 8, 8, 24, device=dev(), dtype=torch.bfloat16),
                                torch.zeros(1, 64, 24, device=dev(), dtype=torch.bfloat16),
                                torch.zeros(1, 64, 2, device=dev(), dtype=torch.int64), 3, 5)
+
+
+def test_refine_tiled_kernel_incoherent_and_out_of_range(backend):
+    """n == h*w selects the tiled (bulk-copy staged) kernel.  Random centres make every tile
+    incoherent (global-memory path per query), a coherent half exercises the staged path, and
+    centres far outside the image / beyond int32 must be returned untouched."""
+    h, w, fdim = 40, 56, 24
+    n = h * w
+    g = torch.Generator().manual_seed(5)
+    D11 = torch.nn.functional.normalize(torch.randn(2, h, w, fdim, generator=g), dim=-1).half()
+    D21 = torch.nn.functional.normalize(torch.randn(2, n, fdim, generator=g), dim=-1).half()
+    p1 = torch.stack([torch.randint(0, w, (2, n), generator=g), torch.randint(0, h, (2, n), generator=g)], -1)
+    ident = torch.stack([torch.arange(n) % w, torch.arange(n) // w], -1)
+    p1[1] = (ident + torch.tensor([3, -2])).clamp_min(0)  # coherent shift (second batch row)
+    p1[1, :, 0].clamp_(max=w - 1)
+    p1[1, :, 1].clamp_(max=h - 1)
+    p1[0, :6] = torch.tensor([[-1, 5], [w, 5], [5, -16], [-100, -100], [2 ** 40, 3], [7, -(2 ** 35)]])
+    for dil in (5, 1, 3):
+        (r,) = backend.refine_matches(D11.to(dev()), D21.to(dev()), p1.to(dev()), 3, dil)
+        (r_o,) = oracle.refine_matches(D11, D21, p1, 3, dil)
+        assert torch.equal(r.cpu(), r_o), dil
+    assert torch.equal(r.cpu()[0, 3:6], p1[0, 3:6])
