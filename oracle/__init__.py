@@ -129,3 +129,17 @@ def gauss_newton_points(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_po
                         Q_thresh, max_iter, delta_thresh):
     return _gauss_newton(2, Twc, Xs, Cs, None, ii, jj, idx_ii2jj, valid_match, Q, sigma_point, 1.0,
                          C_thresh, Q_thresh, 0, 0, 0, 0.0, max_iter, delta_thresh)
+
+
+def gn_solve(Hs, gs, ii_opt, jj_opt, M):
+    """SparseBlock assembly + LLT solve (gn_kernels.cu:56-158): dx (M,7) f32, ok flag."""
+    E = ii_opt.shape[0]
+    dx = torch.zeros(M, 7, dtype=torch.float32)
+    ok = lib().oracle_gn_solve(_p(_cpu(Hs, torch.float32)), _p(_cpu(gs, torch.float32)),
+                               _p(_cpu(ii_opt, torch.int64)), _p(_cpu(jj_opt, torch.int64)), E, M, _p(dx))
+    return dx, bool(ok)
+
+
+def pose_retr(Twc, dx, num_fix=1):
+    """pose_retr_kernel (gn_kernels.cu:414-452), in place."""
+    lib().oracle_pose_retr(_p(_cpu(Twc, torch.float32)), _p(_cpu(dx, torch.float32)), Twc.shape[0], num_fix)

@@ -175,9 +175,9 @@ extern "C" int b200slam_refine_matches_f16(const void *D11, const void *D21, con
   // Tiled kernel with bulk-copy staged windows: queries form the (h, w) pixel grid of view 2
   // (n == h*w, as in matching.py:79-85), radius 3, and the nominal box of the coarsest level fits.
   const int reach = radius * dilation_max;
-  const long long nominal = (long long)(rtile::TW + 2 * reach + 4) * (rtile::TH + 2 * reach + 4) * fdim * 2;
+  const long long nominal = (long long)(rtile::TW + 2 * reach + 2) * (rtile::TH + 2 * reach + 2) * fdim * 2;
   if (fdim == 24 && aligned && radius == 3 && n == h * w && dilation_max >= 1 && nominal <= rtile::BOX_BYTES &&
-      w >= rtile::TW + 2 * reach + 4) {
+      w >= rtile::TW + 2 * reach + 2) {
     static bool attr_set = false;
     if (!attr_set) {
       cudaFuncSetAttribute(rtile::refine_tile_kernel<24, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,

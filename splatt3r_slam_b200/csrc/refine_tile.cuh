@@ -184,7 +184,7 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
         if (x1 >= x0 && y1 >= y0) {
           if ((x1 - x0 + 1) * (y1 - y0 + 1) > MAX_PX) {
             // incoherent tile: keep a box of the nominal size around the mean centre
-            const int side_x = min(TW + 2 * rd + 4, w), side_y = min(min(TH + 2 * rd + 4, h), MAX_PX / side_x);
+            const int side_x = min(TW + 2 * rd + 2, w), side_y = min(min(TH + 2 * rd + 2, h), MAX_PX / side_x);
             const int cx = su / c, cy = sv / c;
             x0 = min(max(cx - side_x / 2, 0), w - side_x); x1 = x0 + side_x - 1;
             y0 = min(max(cy - side_y / 2, 0), h - side_y); y1 = y0 + side_y - 1;

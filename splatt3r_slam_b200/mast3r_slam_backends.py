@@ -237,7 +237,11 @@ def gn_build_blocks(prm, Twc, Xs, Cs, K, ii, jj, idx, valid, Q):
 
 
 def gn_status(device):
-    ws = _workspaces[(device.type, device.index)]
+    return gn_status_ws(_workspaces[(device.type, device.index)])
+
+
+def gn_status_ws(ws):
+    device = ws.device
     it, dn, cf = ctypes.c_int(), ctypes.c_int(), ctypes.c_int()
     _check(_lib.b200slam_gn_status(ws.data_ptr(), ctypes.byref(it), ctypes.byref(dn), ctypes.byref(cf),
                                    torch.cuda.current_stream(device).cuda_stream), "gn_status")
