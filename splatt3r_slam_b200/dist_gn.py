@@ -141,7 +141,10 @@ def bench_graph(args, rank, world, local):
     chk = T.clone()
     if world > 1:
         dist.broadcast(chk, src=0)
-    same = bool(torch.equal(chk, T))
+    flag = torch.tensor([int(torch.equal(chk, T))], device=dev)
+    if world > 1:
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    same = bool(flag.item())
     if rank != 0:
         return None
     try:
