@@ -8,6 +8,7 @@
 #include <cuda_runtime.h>
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 #include "../../include/b200slam.h"
 #include "gn_build.cuh"
@@ -28,32 +29,53 @@ __device__ __forceinline__ unsigned long long gtimer() {
   return t;
 }
 constexpr size_t STATE_BYTES = 256;
-constexpr int MAX_SPLITS = 296;
 
 __host__ __device__ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Layout {
   size_t partials, edge_blocks, A, rhs, rows, first, total;
-  int S;
 };
 
-inline int choose_splits(int E, int n) {
-  // one CTA per SM (148 SMs; the build kernel's ~140 registers x 256 threads allow 1 CTA/SM), so
-  // small graphs run as a single wave; never fewer than 1024 points per CTA
-  int S = 148 / E;
-  const int maxS = (n + 1023) / 1024;
-  if (S > maxS) S = maxS;
-  if (S > MAX_SPLITS) S = MAX_SPLITS;
-  if (S < 1) S = 1;
-  return S;
+// Number of CTAs (S) that split the n points of one edge when `Ecount` edges are built by one
+// launch.  The build kernel is capped at 128 registers => 2 resident CTAs per SM => 296 slots on
+// 148 SMs.  S is chosen to fill whole waves of 296 (measured on B200, N=32/E=128: 384 CTAs =
+// 1.3 waves ran 27% slower than 256 CTAs), with at least 512 points per CTA.
+// B200SLAM_GN_SPLITS overrides S (tuning aid).
+constexpr int CTA_SLOTS = 296;
+constexpr int MAX_SPLITS = 160;
+inline int choose_splits(int Ecount, int n) {
+  static const int forced = getenv("B200SLAM_GN_SPLITS") ? atoi(getenv("B200SLAM_GN_SPLITS")) : 0;
+  if (Ecount < 1) Ecount = 1;
+  int maxS = (n + 511) / 512;
+  if (maxS > MAX_SPLITS) maxS = MAX_SPLITS;
+  if (maxS < 1) maxS = 1;
+  if (forced > 0) return forced < maxS ? forced : maxS;
+  int best = 1;
+  double best_eff = 0.0;
+  for (int S = 1; S <= maxS; S++) {
+    const long long C = (long long)Ecount * S;
+    const long long waves = (C + CTA_SLOTS - 1) / CTA_SLOTS;
+    const double eff = (double)C / (double)(waves * CTA_SLOTS);
+    if (eff > best_eff + 0.02) { best_eff = eff; best = S; }  // smallest S within 2% of the best fill
+    if (waves >= 8 && eff > 0.9) break;
+  }
+  return best;
+}
+
+inline size_t partial_slots(int E) { return (size_t)E * 2 + 4096; }
+inline int splits_for(int E, int Ecount, int n) {
+  int S = choose_splits(Ecount, n);
+  const size_t cap = partial_slots(E) / (size_t)(Ecount > 0 ? Ecount : 1);
+  if ((size_t)S > cap) S = (int)cap;
+  return S < 1 ? 1 : S;
 }
 
 inline Layout make_layout(int N, int E, int n) {
   Layout L;
-  L.S = choose_splits(E > 0 ? E : 1, n);
   const size_t D = (size_t)7 * (N > 1 ? N - 1 : 1);
   size_t off = STATE_BYTES;
-  L.partials = off; off = align256(off + (size_t)E * L.S * NACC * sizeof(double));
+  // capacity in (edge, split) slots; splits_for() clamps S so that any shard of the E edges fits
+  L.partials = off; off = align256(off + partial_slots(E) * NACC * sizeof(double));
   L.edge_blocks = off; off = align256(off + (size_t)E * 56 * sizeof(double));
   L.A = off; off = align256(off + D * D * sizeof(double));
   L.rhs = off; off = align256(off + D * sizeof(double));
@@ -71,7 +93,7 @@ namespace b200gn {
 
 // ---- stage 1 ----------------------------------------------------------------------------------
 template <int KIND, bool FUSED>
-__global__ void __launch_bounds__(BUILD_THREADS)
+__global__ void __launch_bounds__(BUILD_THREADS, 2)
 build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__ Cs,
              const int64_t *__restrict__ ii_row, const int64_t *__restrict__ jj_row,
              const int64_t *__restrict__ idx, const uint8_t *__restrict__ valid,
@@ -155,7 +177,7 @@ build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__
     double sum = 0.0;
 #pragma unroll
     for (int wq = 0; wq < BUILD_THREADS / 32; wq++) sum += (double)red[wq][threadIdx.x];
-    partials[((size_t)e * S + s) * NACC + threadIdx.x] = sum;
+    partials[((size_t)blockIdx.y * S + s) * NACC + threadIdx.x] = sum;  // slot of the edge WITHIN this launch
   }
   if (FUSED) {
     // last-arriving CTA finishes the iteration: finalize + assemble + solve + retract
@@ -207,7 +229,7 @@ finalize_kernel(const float *__restrict__ Twc, const int64_t *__restrict__ ii_ro
   if (wid >= Ecount) return;
   __shared__ double sc[4][FIN_SCRATCH];
   const int e = e0 + wid;
-  finalize_edge(Twc, ii_row, partials, S, e, edge_blocks + (size_t)e * 56, sc[threadIdx.x >> 5], lane);
+  finalize_edge(Twc, ii_row, partials, S, e, wid, edge_blocks + (size_t)e * 56, sc[threadIdx.x >> 5], lane);
 }
 
 // reference-layout export: Hs (4,E,7,7) f32, gs (2,E,7) f32 (gn_kernels.cu:1119-1132)

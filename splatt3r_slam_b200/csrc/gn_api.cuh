@@ -78,13 +78,14 @@ inline int launch_edge_blocks(const b200slam_gn_params *p, const BuildConsts &C,
                               char *ws, const Layout &L, cudaStream_t st) {
   State *state = reinterpret_cast<State *>(ws);
   double *partials = reinterpret_cast<double *>(ws + L.partials);
-  int rc = launch_build(p, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, e0, Ecount, L.S, partials,
+  const int S = splits_for(E, Ecount, n);  // per launch: a shard of few edges still fills the GPU
+  int rc = launch_build(p, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, e0, Ecount, S, partials,
                         state, st);
   if (rc) return rc;
   if (Ecount > 0) {
     const int warps_per_cta = 4;
     finalize_kernel<<<(Ecount + warps_per_cta - 1) / warps_per_cta, 32 * warps_per_cta, 0, st>>>(
-        Twc, ii_row, partials, L.S, e0, Ecount, edge_blocks, state);
+        Twc, ii_row, partials, S, e0, Ecount, edge_blocks, state);
     rc = (int)cudaGetLastError();
   }
   return rc;
@@ -230,7 +231,7 @@ extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, 
   for (int it = 0; it < max_iter; it++) {
     if (fused) {  // one launch per iteration: the last stage-1 CTA runs stages 2-3
       const FusedArgs F{true, N, E, delta_thresh, dx, eb};
-      rc = launch_build(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, 0, E, L.S,
+      rc = launch_build(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, 0, E, splits_for(E, E, n),
                         reinterpret_cast<double *>(ws + L.partials), reinterpret_cast<State *>(ws), st, F);
       if (rc) return rc;
       continue;

@@ -42,7 +42,7 @@ constexpr int FIN_SCRATCH = 36 + 49 + 49;  // doubles of shared scratch per warp
 // Warp-cooperative stage 2 for one edge: sum the S per-CTA partials in fixed order (fp64),
 // then H_jj = M^T H0 M and g_j = M^T g0 -> out[0..48], out[49..55].
 __device__ inline void finalize_edge(const float *Twc, const int64_t *ii_row, const double *partials, int S,
-                                     int e, double *out, double *sc, int lane) {
+                                     int e, int slot, double *out, double *sc, int lane) {
   double *acc = sc, *M = sc + 36, *T = sc + 36 + 49;
   // lane L owns splits L, L+32, ... (all 35 sums independent -> loads pipeline), then a fixed
   // xor-shuffle tree combines the lanes: deterministic, no serial chain over S.
@@ -51,7 +51,7 @@ __device__ inline void finalize_edge(const float *Twc, const int64_t *ii_row, co
 #pragma unroll
     for (int l = 0; l < NACC; l++) s[l] = 0.0;
     for (int k = lane; k < S; k += 32) {
-      const double *p = partials + ((size_t)e * S + k) * NACC;
+      const double *p = partials + ((size_t)slot * S + k) * NACC;
 #pragma unroll
       for (int l = 0; l < NACC; l++) s[l] += __ldcg(p + l);
     }
@@ -319,7 +319,7 @@ __device__ inline void small_tail(float *Twc, const int64_t *ii_row, const int64
   __shared__ int fail;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int D = 7 * (N - NUM_FIX);
-  for (int e = warp; e < E; e += BUILD_THREADS / 32) finalize_edge(Twc, ii_row, partials, S, e, edge_blocks + (size_t)e * 56, sc[warp], lane);
+  for (int e = warp; e < E; e += BUILD_THREADS / 32) finalize_edge(Twc, ii_row, partials, S, e, e, edge_blocks + (size_t)e * 56, sc[warp], lane);
   __syncthreads();
   if (tid == 0) state->t[1] = gtimer();
   PackedLower L{Ap};

@@ -76,82 +76,7 @@ repack_planar_kernel(const float *__restrict__ rays_img, float *__restrict__ pla
   }
 }
 
-// One thread per query pixel; planes (9, h*w) of batch row blockIdx.y.
-__global__ void __launch_bounds__(IP_THREADS)
-iter_proj_kernel(const float *__restrict__ planes, const float *__restrict__ pts,
-                 const float *__restrict__ p_init, float *__restrict__ p_new,
-                 uint8_t *__restrict__ converged, int h, int w, int n, int max_iter,
-                 float lambda_init, float cost_thresh) {
-  const int q = blockIdx.x * IP_THREADS + threadIdx.x;
-  if (q >= n) return;
-  const size_t bq = (size_t)blockIdx.y * n + q;
-  const int hw = h * w;
-  const float *img = planes + (size_t)blockIdx.y * hw * 9;
-
-  const float2 pi = __ldg(reinterpret_cast<const float2 *>(p_init) + bq);
-  const float umax = (float)(w - 2), vmax = (float)(h - 2);
-  float u = clampf(pi.x, 1.0f, umax);
-  float v = clampf(pi.y, 1.0f, vmax);
-  const float p0 = __ldg(pts + bq * 3 + 0), p1 = __ldg(pts + bq * 3 + 1), p2 = __ldg(pts + bq * 3 + 2);
-
-  float lambda = lambda_init;
-  bool conv = false;
-  for (int it = 0; it < max_iter; it++) {
-    const int u11 = (int)floorf(u), v11 = (int)floorf(v);
-    const Weights k = bilinear_weights(__fsub_rn(u, (float)u11), __fsub_rn(v, (float)v11));
-    const float *top = img + v11 * w + u11;  // (v,u); +1 = (v,u+1); +w = (v+1,u); +w+1 = (v+1,u+1)
-    float c[9];
-#pragma unroll
-    for (int j = 0; j < 9; j++) {
-      const float *pj = top + (size_t)j * hw;
-      c[j] = tap(k, __ldg(pj + w + 1), __ldg(pj + w), __ldg(pj + 1), __ldg(pj));
-    }
-    const float nrm = __fsqrt_rn(dot3(c[0], c[1], c[2], c[0], c[1], c[2]));
-    const float inv = __frcp_rn(nrm);
-    const float e0 = __fmaf_rn(c[0], inv, -p0), e1 = __fmaf_rn(c[1], inv, -p1),
-                e2 = __fmaf_rn(c[2], inv, -p2);
-    const float cost = dot3(e0, e1, e2, e0, e1, e2);
-    float A00 = dot3(c[3], c[4], c[5], c[3], c[4], c[5]);
-    const float A01 = dot3(c[3], c[4], c[5], c[6], c[7], c[8]);
-    float A11 = dot3(c[6], c[7], c[8], c[6], c[7], c[8]);
-    const float s0 = dot3(e0, e1, e2, c[3], c[4], c[5]);
-    const float s1 = dot3(e0, e1, e2, c[6], c[7], c[8]);
-    A00 = __fadd_rn(A00, lambda);
-    A11 = __fadd_rn(A11, lambda);
-    const float det = __fmaf_rn(A00, A11, -__fmul_rn(A01, A01));
-    const float dinv = __frcp_rn(det);
-    const float nu = __fmaf_rn(A01, s1, -__fmul_rn(s0, A11));
-    const float nv = __fmaf_rn(A01, s0, -__fmul_rn(s1, A00));
-    const float un = clampf(__fmaf_rn(nu, dinv, u), 1.0f, umax);
-    const float vn = clampf(__fmaf_rn(nv, dinv, v), 1.0f, vmax);
-
-    const int u2 = (int)floorf(un), v2 = (int)floorf(vn);
-    const Weights k2 = bilinear_weights(__fsub_rn(un, (float)u2), __fsub_rn(vn, (float)v2));
-    const float *top2 = img + v2 * w + u2;
-    float d[3];
-#pragma unroll
-    for (int j = 0; j < 3; j++) {
-      const float *pj = top2 + (size_t)j * hw;
-      d[j] = tap(k2, __ldg(pj + w + 1), __ldg(pj + w), __ldg(pj + 1), __ldg(pj));
-    }
-    const float nrm2 = __fsqrt_rn(dot3(d[0], d[1], d[2], d[0], d[1], d[2]));
-    const float inv2 = __frcp_rn(nrm2);
-    const float f0 = __fmaf_rn(d[0], inv2, -p0), f1 = __fmaf_rn(d[1], inv2, -p1),
-                f2 = __fmaf_rn(d[2], inv2, -p2);
-    const float new_cost = dot3(f0, f1, f2, f0, f1, f2);
-    if (new_cost < cost) {
-      u = un;
-      v = vn;
-      lambda = __double2float_rn(__dmul_rn((double)lambda, 0.1));  // matching_kernels.cu:261
-      conv = new_cost < cost_thresh;
-    } else {
-      lambda = __fmul_rn(lambda, 10.0f);
-      conv = cost < cost_thresh;
-    }
-  }
-  reinterpret_cast<float2 *>(p_new)[bq] = make_float2(u, v);
-  converged[bq] = conv ? 1 : 0;
-}
+#include "iter_proj_kernel.cuh"
 
 }  // namespace
 
