@@ -22,6 +22,7 @@ struct State {  // head of the workspace
   int chol_fail;  // number of failed factorisations (dx = 0)
   unsigned ticket;  // arrival counter of the fused small-problem path (reset by the last CTA)
   unsigned long long t[4];  // %globaltimer stamps of the last fused tail: start, finalized, solved, end
+  unsigned gen;  // grid-barrier generation of the persistent kernel (= iterations completed)
 };
 __device__ __forceinline__ unsigned long long gtimer() {
   unsigned long long t;
@@ -191,7 +192,7 @@ build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__
     __syncthreads();
     if (!is_last) return;
     if (threadIdx.x == 0) { state->ticket = 0; state->t[0] = gtimer(); }
-    small_tail(Twc, ii_row, jj_row, partials, S, E, N, delta_thresh, dx, edge_blocks, state);
+    small_tail<BUILD_THREADS>(Twc, ii_row, jj_row, partials, S, E, N, delta_thresh, dx, edge_blocks, state);
   }
 }
 
@@ -252,4 +253,5 @@ __global__ void export_blocks_kernel(const double *__restrict__ edge_blocks, int
 
 }  // namespace b200gn
 
+#include "gn_persistent.cuh"
 #include "gn_api.cuh"

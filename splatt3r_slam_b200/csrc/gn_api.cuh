@@ -121,6 +121,50 @@ inline int launch_solve(float *Twc, const int64_t *ii_row, const int64_t *jj_row
   return (int)cudaGetLastError();
 }
 
+// Persistent single-launch GN loop (gn_persistent.cuh).  Returns 1 when the problem does not qualify
+// (caller falls back to one launch per iteration), 0 on success, a CUDA error otherwise.
+template <int KIND>
+inline int launch_persistent_kind(dim3 grid, size_t smem, cudaStream_t st, void **args) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t err = cudaFuncSetAttribute(gn_persistent_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           PERSIST_WORDS * PERSIST_MAX_POINTS * (int)sizeof(float));
+    if (err != cudaSuccess) return (int)err;
+    attr_set = true;
+  }
+  return (int)cudaLaunchCooperativeKernel((const void *)gn_persistent_kernel<KIND>, grid, dim3(PERSIST_THREADS), args,
+                                          smem, st);
+}
+
+inline int try_persistent(const b200slam_gn_params *p, BuildConsts C, float *Twc, const float *Xs, const float *Cs,
+                          const int64_t *ii_row, const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                          const float *Q, int N, int E, int n, int max_iter, float delta_thresh, float *dx,
+                          double *partials, double *edge_blocks, State *state, cudaStream_t st) {
+  static const bool disabled = getenv("B200SLAM_GN_NO_PERSIST") != nullptr;  // tuning aid
+  static int num_sms = 0;
+  if (num_sms == 0) {
+    int dev = 0, coop = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    if (!coop) num_sms = -1;
+  }
+  if (disabled || num_sms < 1 || E < 1 || E > num_sms || (n & 3) || max_iter < 1) return 1;
+  const int S = num_sms / E;  // one CTA per SM, all co-resident
+  const int groups = n >> 2, gper = (groups + S - 1) / S;
+  if (4 * gper > PERSIST_MAX_POINTS || (size_t)E * S > partial_slots(E)) return 1;
+  const size_t smem = (size_t)PERSIST_WORDS * 4 * gper * sizeof(float);
+  void *args[] = {&Twc, &Xs, &Cs, &ii_row, &jj_row, &idx, &valid, &Q, &n, &C, &partials, &state,
+                  &N, &E, &max_iter, &delta_thresh, &dx, &edge_blocks};
+  dim3 grid(S, E);
+  switch (p->kind) {
+    case B200SLAM_GN_RAYS: return launch_persistent_kind<B200SLAM_GN_RAYS>(grid, smem, st, args);
+    case B200SLAM_GN_CALIB: return launch_persistent_kind<B200SLAM_GN_CALIB>(grid, smem, st, args);
+    case B200SLAM_GN_POINTS: return launch_persistent_kind<B200SLAM_GN_POINTS>(grid, smem, st, args);
+  }
+  return B200SLAM_EINVAL;
+}
+
 inline bool bad_args(const b200slam_gn_params *p, const void *Twc, const void *Xs, const void *Cs,
                      const void *ii, const void *jj, const void *idx, const void *valid, const void *Q,
                      int N, int E, int n, const void *ws) {
@@ -228,6 +272,11 @@ extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, 
   if (rc) return rc;
   double *eb = reinterpret_cast<double *>(ws + L.edge_blocks);
   const bool fused = 7 * (N - NUM_FIX) <= SMALL_MAX_D && E <= SMALL_MAX_E;
+  if (fused) {  // small graph whose points fit in shared memory: the whole loop is one cooperative launch
+    rc = try_persistent(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, N, E, n, max_iter, delta_thresh, dx,
+                        reinterpret_cast<double *>(ws + L.partials), eb, reinterpret_cast<State *>(ws), st);
+    if (rc != 1) return rc;
+  }
   for (int it = 0; it < max_iter; it++) {
     if (fused) {  // one launch per iteration: the last stage-1 CTA runs stages 2-3
       const FusedArgs F{true, N, E, delta_thresh, dx, eb};

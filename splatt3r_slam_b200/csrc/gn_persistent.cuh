@@ -1,0 +1,162 @@
+// b200slam — persistent Gauss-Newton kernel for small graphs (the tracker: N = 2, E = 2).
+//
+// When all E*n points fit in the shared memory of the 148 SMs (32 B per point; 512x384 pairs:
+// E <= 4), the WHOLE max_iter loop is ONE cooperative launch:
+//   prologue   every CTA loads its slice of the edge's points ONCE — streams valid/idx/Q/Xj/Cj,
+//              gathers the matched Xi/Ci, folds the iteration-independent validity test
+//              (match & q > Q_thr & ci > C_thr & cj > C_thr) — into shared memory (SoA, 8 words/point)
+//   iteration  relative pose from the current Twc -> 35 accumulators from shared memory -> CTA
+//              partial (fp64) -> ticket; the last-arriving CTA runs stages 2-3 (finalize, assemble,
+//              fp64 Cholesky, retraction, convergence flag: small_tail) and releases a generation
+//              counter the other CTAs spin on (they are co-resident: cooperative launch, 1 CTA/SM).
+// Per iteration this replaces a kernel launch + 17.7 MB of L2/HBM reads + dependent gathers by a
+// grid barrier + shared-memory reads (measured on B200: see DESIGN.md section 5).
+#pragma once
+
+namespace b200gn {
+
+constexpr int PERSIST_WORDS = 8;           // Xi(3) Xj(3) q ind
+constexpr int PERSIST_MAX_POINTS = 5632;   // per CTA: 176 KB of dynamic shared memory
+constexpr int PERSIST_THREADS = 512;
+
+__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_u32(unsigned *p, unsigned v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+template <int KIND>
+__global__ void __launch_bounds__(PERSIST_THREADS, 1)
+gn_persistent_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__ Cs,
+                     const int64_t *__restrict__ ii_row, const int64_t *__restrict__ jj_row,
+                     const int64_t *__restrict__ idx, const uint8_t *__restrict__ valid,
+                     const float *__restrict__ Q, int n, BuildConsts C, double *partials, State *state,
+                     int N, int E, int max_iter, float delta_thresh, float *dx, double *edge_blocks) {
+  extern __shared__ __align__(16) float pts_sm[];
+  __shared__ float pose_sm[16];
+  __shared__ int flag_sm;
+  if (KIND == B200SLAM_GN_CALIB) {  // gn_kernels.cu:1273-1278
+    C.fx = __ldg(C.Kptr + 0); C.fy = __ldg(C.Kptr + 4); C.cx = __ldg(C.Kptr + 2); C.cy = __ldg(C.Kptr + 5);
+  }
+  const int e = blockIdx.y, S = gridDim.x, s = blockIdx.x, tid = threadIdx.x;
+  const int ix = (int)ii_row[e], jx = (int)jj_row[e];
+  const int groups = n >> 2;  // host guarantees n % 4 == 0
+  const int gper = (groups + S - 1) / S;
+  const int g_begin = s * gper, g_end = min(groups, g_begin + gper);
+  const int stride = 4 * gper;  // points per smem array
+  const int npts = 4 * max(g_end - g_begin, 0);
+
+  // ---- prologue: stage this CTA's points ---------------------------------------------------------
+  {
+    const float *Xi_base = Xs + (size_t)ix * n * 3, *Xj_base = Xs + (size_t)jx * n * 3;
+    const float *Ci_base = Cs + (size_t)ix * n, *Cj_base = Cs + (size_t)jx * n;
+    const int64_t *idx_e = idx + (size_t)e * n;
+    const uint8_t *val_e = valid + (size_t)e * n;
+    const float *Q_e = Q + (size_t)e * n;
+    for (int g = g_begin + tid; g < g_end; g += PERSIST_THREADS) {
+      const uint32_t vm4 = __ldg(reinterpret_cast<const uint32_t *>(val_e) + g);
+      const longlong2 ia = __ldg(reinterpret_cast<const longlong2 *>(idx_e) + 2 * g);
+      const longlong2 ib = __ldg(reinterpret_cast<const longlong2 *>(idx_e) + 2 * g + 1);
+      const float4 q4 = __ldg(reinterpret_cast<const float4 *>(Q_e) + g);
+      const float4 c4 = __ldg(reinterpret_cast<const float4 *>(Cj_base) + g);
+      const float4 xa = __ldg(reinterpret_cast<const float4 *>(Xj_base) + 3 * g);
+      const float4 xb = __ldg(reinterpret_cast<const float4 *>(Xj_base) + 3 * g + 1);
+      const float4 xc = __ldg(reinterpret_cast<const float4 *>(Xj_base) + 3 * g + 2);
+      const long long ind[4] = {ia.x, ia.y, ib.x, ib.y};
+      const float qq[4] = {q4.x, q4.y, q4.z, q4.w};
+      const float cj[4] = {c4.x, c4.y, c4.z, c4.w};
+      float Xi[4][3], qs[4];
+      int iw[4];
+#pragma unroll
+      for (int t = 0; t < 4; t++) {
+        const bool vm = (vm4 >> (8 * t)) & 0xffu;
+        const long long id = vm ? ind[t] : 0;  // gn_kernels.cu:912-913
+        Xi[t][0] = __ldg(Xi_base + 3 * id);
+        Xi[t][1] = __ldg(Xi_base + 3 * id + 1);
+        Xi[t][2] = __ldg(Xi_base + 3 * id + 2);
+        const float ci = __ldg(Ci_base + id);
+        const bool ok = vm && (qq[t] > C.Q_thresh) && (ci > C.C_thresh) && (cj[t] > C.C_thresh);
+        qs[t] = ok ? qq[t] : -INFINITY;  // fails "q > Q_thresh" in point_contrib => point skipped
+        iw[t] = (int)ind[t];
+      }
+      const int p = 4 * (g - g_begin);
+      float4 *a = reinterpret_cast<float4 *>(pts_sm + p);
+      const int st4 = stride >> 2;
+      a[0 * st4] = make_float4(Xi[0][0], Xi[1][0], Xi[2][0], Xi[3][0]);
+      a[1 * st4] = make_float4(Xi[0][1], Xi[1][1], Xi[2][1], Xi[3][1]);
+      a[2 * st4] = make_float4(Xi[0][2], Xi[1][2], Xi[2][2], Xi[3][2]);
+      a[3 * st4] = make_float4(xa.x, xa.w, xb.z, xc.y);
+      a[4 * st4] = make_float4(xa.y, xb.x, xb.w, xc.z);
+      a[5 * st4] = make_float4(xa.z, xb.y, xc.x, xc.w);
+      a[6 * st4] = make_float4(qs[0], qs[1], qs[2], qs[3]);
+      a[7 * st4] = make_float4(__int_as_float(iw[0]), __int_as_float(iw[1]), __int_as_float(iw[2]),
+                               __int_as_float(iw[3]));
+    }
+  }
+  __syncthreads();
+
+  // ---- iterations ----------------------------------------------------------------------------------
+  const unsigned total = gridDim.x * gridDim.y;
+  const int lane = tid & 31, warp = tid >> 5;
+  __shared__ float red[PERSIST_THREADS / 32][NACC];
+  __shared__ bool is_last;
+  for (int it = 0; it < max_iter; it++) {
+    // current poses of the edge's two keyframes, straight from L2 (another SM's tail wrote them)
+    if (tid < 16) pose_sm[tid] = __ldcg(Twc + 8 * (tid < 8 ? ix : jx) + (tid & 7));
+    __syncthreads();
+    const EdgePose P = rel_pose(pose_sm, pose_sm + 8);
+
+    float acc[NACC];
+#pragma unroll
+    for (int l = 0; l < NACC; l++) acc[l] = 0.0f;
+    for (int p = tid; p < npts; p += PERSIST_THREADS) {
+      const float q = pts_sm[6 * stride + p];
+      if (!(q > C.Q_thresh)) continue;
+      const float Xi[3] = {pts_sm[p], pts_sm[stride + p], pts_sm[2 * stride + p]};
+      const float Xj[3] = {pts_sm[3 * stride + p], pts_sm[4 * stride + p], pts_sm[5 * stride + p]};
+      const long long ind = (long long)__float_as_int(pts_sm[7 * stride + p]);
+      point_contrib<KIND>(acc, P, C, Xi, INFINITY, Xj, INFINITY, q, ind);
+    }
+    // warp tree (fp32) -> cross-warp sum (fp64, fixed order) -> per-CTA partial
+#pragma unroll
+    for (int l = 0; l < NACC; l++) {
+      float v = acc[l];
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (lane == 0) red[warp][l] = v;
+    }
+    __syncthreads();
+    if (tid < NACC) {
+      double sum = 0.0;
+#pragma unroll
+      for (int wq = 0; wq < PERSIST_THREADS / 32; wq++) sum += (double)red[wq][tid];
+      partials[((size_t)e * S + s) * NACC + tid] = sum;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      cuda::atomic_ref<unsigned, cuda::thread_scope_device> ticket(state->ticket);
+      is_last = ticket.fetch_add(1u, cuda::memory_order_acq_rel) == total - 1;
+    }
+    __syncthreads();
+    if (is_last) {
+      if (tid == 0) { state->ticket = 0; state->t[0] = gtimer(); }
+      small_tail<PERSIST_THREADS>(Twc, ii_row, jj_row, partials, S, E, N, delta_thresh, dx, edge_blocks, state);
+      __syncthreads();
+      if (tid == 0) {
+        flag_sm = state->done;
+        __threadfence();
+        st_release_u32(&state->gen, (unsigned)(it + 1));  // opens the grid barrier
+      }
+    } else if (tid == 0) {
+      while (ld_acquire_u32(&state->gen) < (unsigned)(it + 1)) __nanosleep(20);
+      flag_sm = __ldcg(&state->done);
+    }
+    __syncthreads();
+    if (flag_sm) break;  // ||dx|| < delta: same early exit on every CTA
+  }
+}
+
+}  // namespace b200gn

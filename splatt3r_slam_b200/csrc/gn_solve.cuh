@@ -202,6 +202,12 @@ struct FullLower {
 // not positive (the reference's "solver.info() != Success" => dx = 0, :141-149).
 // x (length D, shared) holds the rhs on entry and the solution on exit; col is scratch (D).
 // WARP = true: executed by the 32 threads of warp 0 only (D <= 32), __syncwarp instead of barriers.
+//
+// Two barriers per column: every thread reads the pivot itself and forms 1/sqrt(d) (no
+// broadcast step), L(j,j) stores that RECIPROCAL (the triangular solves multiply by it), and
+// the forward substitution L y = b rides along as one more row of the trailing update.  The
+// backward substitution is done by warp 0 alone with warp-level synchronisation (D <= 256).
+constexpr int CHOL_UNROLL = 7;  // register-blocked trailing update for D <= 224
 template <class Mat, bool WARP = false>
 __device__ bool cholesky_solve(Mat L, int D, double *x, double *col, int *fail) {
 #define CHOL_SYNC() do { if (WARP) __syncwarp(); else __syncthreads(); } while (0)
@@ -210,42 +216,78 @@ __device__ bool cholesky_solve(Mat L, int D, double *x, double *col, int *fail) 
   if (tid == 0) *fail = 0;
   CHOL_SYNC();
   for (int j = 0; j < D; j++) {
-    if (tid == 0) {
-      const double d = L.at(j, j);
-      if (!(d > 0.0)) *fail = 1;
-      else L.at(j, j) = sqrt(d);
+    const double d = L.at(j, j);  // final: the previous column's trailing update is behind a barrier
+    if (!(d > 0.0)) {             // uniform: every thread sees the same pivot
+      if (tid == 0) *fail = 1;
+      return false;
     }
-    CHOL_SYNC();
-    if (*fail) return false;
-    const double dinv = 1.0 / L.at(j, j);
+    const double dinv = rsqrt(d);
+    const double yj = x[j] * dinv;  // forward substitution, column-oriented
     for (int i = j + 1 + tid; i < D; i += T) {
       const double v = L.at(i, j) * dinv;
       L.at(i, j) = v;
       col[i] = v;
+      x[i] -= v * yj;
     }
-    CHOL_SYNC();
+    CHOL_SYNC();  // col[] complete; everyone has read L(j,j) and x[j]
+    if (tid == 0) {
+      L.at(j, j) = dinv;
+      x[j] = yj;
+    }
     // trailing update: row i (one warp per row), k over lanes
-    for (int i = j + 1 + warp; i < D; i += nwarp) {
-      const double ci = col[i];
-      for (int k = j + 1 + lane; k <= i; k += 32) L.at(i, k) -= ci * col[k];
+    if (D <= 32 * CHOL_UNROLL) {
+      // a lane owns columns k = j+1+lane+32m: its col[k] stay in registers for the whole column
+      // step, and a row's loads are all issued before its FMAs/stores (the plain loop below
+      // serialises on possible aliasing of L and col: measured 1.6 us per column at D = 217)
+      double ck[CHOL_UNROLL];
+#pragma unroll
+      for (int m = 0; m < CHOL_UNROLL; m++) {
+        const int k = j + 1 + lane + 32 * m;
+        ck[m] = k < D ? col[k] : 0.0;
+      }
+      for (int i = j + 1 + warp; i < D; i += nwarp) {
+        const double ci = col[i];
+        double *row = &L.at(i, 0);
+        double v[CHOL_UNROLL];
+#pragma unroll
+        for (int m = 0; m < CHOL_UNROLL; m++) {
+          const int k = j + 1 + lane + 32 * m;
+          if (k <= i) v[m] = row[k];
+        }
+#pragma unroll
+        for (int m = 0; m < CHOL_UNROLL; m++) {
+          const int k = j + 1 + lane + 32 * m;
+          if (k <= i) row[k] = v[m] - ci * ck[m];
+        }
+      }
+    } else {
+      for (int i = j + 1 + warp; i < D; i += nwarp) {
+        const double ci = col[i];
+        for (int k = j + 1 + lane; k <= i; k += 32) L.at(i, k) -= ci * col[k];
+      }
     }
-    CHOL_SYNC();
-  }
-  // forward: L y = b
-  for (int j = 0; j < D; j++) {
-    if (tid == 0) x[j] = x[j] / L.at(j, j);
-    CHOL_SYNC();
-    const double yj = x[j];
-    for (int i = j + 1 + tid; i < D; i += T) x[i] -= L.at(i, j) * yj;
     CHOL_SYNC();
   }
   // backward: L^T x = y
-  for (int j = D - 1; j >= 0; j--) {
-    if (tid == 0) x[j] = x[j] / L.at(j, j);
+  if (WARP || D <= 256) {
+    if (warp == 0) {
+      for (int j = D - 1; j >= 0; j--) {
+        const double xj = x[j] * L.at(j, j);
+        __syncwarp();
+        if (lane == 0) x[j] = xj;
+        for (int i = lane; i < j; i += 32) x[i] -= L.at(j, i) * xj;
+        __syncwarp();
+      }
+    }
     CHOL_SYNC();
-    const double xj = x[j];
-    for (int i = tid; i < j; i += T) x[i] -= L.at(j, i) * xj;
-    CHOL_SYNC();
+  } else {
+    for (int j = D - 1; j >= 0; j--) {
+      const double xj = x[j] * L.at(j, j);
+      CHOL_SYNC();
+      if (tid == 0) x[j] = xj;
+      for (int i = tid; i < j; i += T) x[i] -= L.at(j, i) * xj;
+      CHOL_SYNC();
+    }
   }
   return true;
 #undef CHOL_SYNC
@@ -289,20 +331,27 @@ solve_retract_kernel(float *__restrict__ Twc, double *__restrict__ A, const doub
   double *x = sm, *col = sm + Dp;  // Dp = max(D, 32): col doubles as the cross-warp scratch
   __shared__ int fail;
   const int tid = threadIdx.x;
+  if (tid == 0) state->t[0] = gtimer();
   for (int i = tid; i < D; i += blockDim.x) x[i] = rhs[i];
   bool ok;
   if (PACKED) {
     PackedLower L{sm + 2 * Dp};
-    for (int i = 0; i < D; i++)
-      for (int k = tid; k <= i; k += blockDim.x) L.at(i, k) = A[(size_t)i * D + k];
+    // one thread per element of the lower triangle (flat index -> (i,k)), coalesced along rows
+    for (int t = tid; t < D * D; t += blockDim.x) {
+      const int i = t / D, k = t - i * D;
+      if (k <= i) L.at(i, k) = A[t];
+    }
     __syncthreads();
+    if (tid == 0) state->t[1] = gtimer();
     ok = cholesky_solve(L, D, x, col, &fail);
+    if (tid == 0) state->t[2] = gtimer();
   } else {
     FullLower L{A, D};
     __syncthreads();
     ok = cholesky_solve(L, D, x, col, &fail);
   }
   finish_update(ok, x, col, D, N, Twc, dx, delta_thresh, state);
+  if (tid == 0) state->t[3] = gtimer();
 }
 
 // ---- fused tail for small problems (D <= SMALL_MAX_D): executed by the LAST stage-1 CTA of an
@@ -310,20 +359,123 @@ solve_retract_kernel(float *__restrict__ Twc, double *__restrict__ A, const doub
 constexpr int SMALL_MAX_D = 63;   // N <= 10 poses
 constexpr int SMALL_MAX_E = 96;
 
+// Column c of the rotation matrix of unit quaternion q (xyzw), fp64 (actSO3 on a unit vector).
+__device__ __forceinline__ void rot_col(const double *q, int c, double *Y) {
+  const double X[3] = {c == 0 ? 1.0 : 0.0, c == 1 ? 1.0 : 0.0, c == 2 ? 1.0 : 0.0};
+  const double uv0 = 2.0 * (q[1] * X[2] - q[2] * X[1]);
+  const double uv1 = 2.0 * (q[2] * X[0] - q[0] * X[2]);
+  const double uv2 = 2.0 * (q[0] * X[1] - q[1] * X[0]);
+  Y[0] = X[0] + q[3] * uv0 + (q[1] * uv2 - q[2] * uv1);
+  Y[1] = X[1] + q[3] * uv1 + (q[2] * uv0 - q[0] * uv2);
+  Y[2] = X[2] + q[3] * uv2 + (q[0] * uv1 - q[1] * uv0);
+}
+// One entry M[k][c] of adj_inv_matrix (same expressions), so that 49 threads build M at once.
+__device__ __forceinline__ double adj_inv_entry(const float *Ti, int k, int c) {
+  if (k == 6) return c == 6 ? 1.0 : 0.0;
+  const double q[4] = {Ti[3], Ti[4], Ti[5], Ti[6]};
+  double Ra[3];
+  rot_col(q, k < 3 ? k : k - 3, Ra);
+  if (k >= 3) return (c >= 3 && c < 6) ? Ra[c - 3] : 0.0;
+  const double t[3] = {Ti[0], Ti[1], Ti[2]};
+  const double s_inv = 1.0 / (double)Ti[7];
+  switch (c) {
+    case 0: case 1: case 2: return s_inv * Ra[c];
+    case 3: return s_inv * (t[1] * Ra[2] - t[2] * Ra[1]);
+    case 4: return s_inv * (t[2] * Ra[0] - t[0] * Ra[2]);
+    case 5: return s_inv * (t[0] * Ra[1] - t[1] * Ra[0]);
+    default: return s_inv * (t[0] * Ra[0] + t[1] * Ra[1] + t[2] * Ra[2]);
+  }
+}
+
+// Stage 2 for up to 8 edges by the whole CTA (256 threads) instead of one warp per edge: the S
+// partials of every (edge, accumulator) pair are summed by NC threads in interleaved chunks and
+// combined in fixed order; M is built one entry per thread.  sc[e] = [acc 36 | M 49 | T 49].
+// out: (E,56) doubles [H_jj | g_j].  Deterministic (fixed summation order).
+constexpr int SMALL_FIN_E = 8;
+template <int NT>
+__device__ inline void finalize_small(const float *Twc, const int64_t *ii_row, const double *partials, int S, int E,
+                                      double *out, double (*sc)[FIN_SCRATCH], double *tmp) {
+  const int tid = threadIdx.x, items = E * NACC;
+  const int NC = NT / items > 0 ? NT / items : 1;
+  for (int t = tid; t < items * NC; t += NT) {
+    const int item = t % items, chunk = t / items, e = item / NACC, l = item - e * NACC;
+    const double *p = partials + (size_t)e * S * NACC + l;
+    double sum = 0.0;
+    for (int k0 = chunk; k0 < S; k0 += 8 * NC) {  // 8 independent loads in flight per round trip
+      double v[8];
+#pragma unroll
+      for (int u = 0; u < 8; u++) {
+        const int k = k0 + u * NC;
+        v[u] = k < S ? __ldcg(p + (size_t)k * NACC) : 0.0;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; u++) sum += v[u];
+    }
+    tmp[t] = sum;
+  }
+  for (int t = tid; t < E * 49; t += NT) {
+    const int e = t / 49, o = t - e * 49;
+    sc[e][36 + o] = adj_inv_entry(Twc + 8 * (int)ii_row[e], o / 7, o % 7);
+  }
+  __syncthreads();
+  for (int t = tid; t < items; t += NT) {
+    double s = 0.0;
+    for (int c = 0; c < NC; c++) s += tmp[c * items + t];
+    sc[t / NACC][t % NACC] = s;
+  }
+  __syncthreads();
+  for (int t = tid; t < E * 49; t += NT) {  // T = H0 * M
+    const int e = t / 49, o = t - e * 49, a = o / 7, c = o % 7;
+    const double *acc = sc[e], *M = sc[e] + 36;
+    double s = 0.0;
+#pragma unroll
+    for (int k = 0; k < 7; k++) {
+      const int lo = a < k ? a : k, hi = a < k ? k : a;
+      s += acc[lo * 7 - lo * (lo - 1) / 2 + (hi - lo)] * M[k * 7 + c];
+    }
+    sc[e][36 + 49 + o] = s;
+  }
+  __syncthreads();
+  for (int t = tid; t < E * 56; t += NT) {  // H_jj = M^T T, g_j = M^T g0
+    const int e = t / 56, o = t - e * 56;
+    const double *acc = sc[e], *M = sc[e] + 36, *T = sc[e] + 36 + 49;
+    double s = 0.0;
+    if (o < 49) {
+      const int r = o / 7, c = o % 7;
+#pragma unroll
+      for (int k = 0; k < 7; k++) s += M[k * 7 + r] * T[k * 7 + c];
+    } else {
+      const int r = o - 49;
+#pragma unroll
+      for (int k = 0; k < 7; k++) s += M[k * 7 + r] * acc[28 + k];
+    }
+    out[t] = s;
+  }
+  __syncthreads();
+}
+
+template <int NT>
 __device__ inline void small_tail(float *Twc, const int64_t *ii_row, const int64_t *jj_row,
                                   const double *partials, int S, int E, int N, float delta_thresh, float *dx,
                                   double *edge_blocks, State *state) {
-  __shared__ double sc[BUILD_THREADS / 32][FIN_SCRATCH];
+  __shared__ double sc[SMALL_FIN_E][FIN_SCRATCH];
   __shared__ double Ap[SMALL_MAX_D * (SMALL_MAX_D + 1) / 2];
   __shared__ double xs[64], cols[64];
   __shared__ int fail;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int D = 7 * (N - NUM_FIX);
-  for (int e = warp; e < E; e += BUILD_THREADS / 32) finalize_edge(Twc, ii_row, partials, S, e, e, edge_blocks + (size_t)e * 56, sc[warp], lane);
-  __syncthreads();
+  __shared__ double ebs[SMALL_FIN_E * 56], fin_tmp[NT];
+  if (E <= SMALL_FIN_E) {  // few edges (the tracker): whole-CTA stage 2, blocks stay in shared memory
+    finalize_small<NT>(Twc, ii_row, partials, S, E, ebs, sc, fin_tmp);
+    edge_blocks = ebs;
+  } else {
+    if (warp < SMALL_FIN_E)
+      for (int e = warp; e < E; e += SMALL_FIN_E) finalize_edge(Twc, ii_row, partials, S, e, e, edge_blocks + (size_t)e * 56, sc[warp], lane);
+    __syncthreads();
+  }
   if (tid == 0) state->t[1] = gtimer();
   PackedLower L{Ap};
-  for (int t = tid; t < D * D; t += BUILD_THREADS) {
+  for (int t = tid; t < D * D; t += NT) {
     const int r = t / D, c = t % D;
     if (c > r) continue;
     const int br = r / 7, kr = r % 7, bc = c / 7, kc = c % 7;
@@ -338,7 +490,7 @@ __device__ inline void small_tail(float *Twc, const int64_t *ii_row, const int64
     }
     L.at(r, c) = s;
   }
-  for (int r = tid; r < D; r += BUILD_THREADS) {
+  for (int r = tid; r < D; r += NT) {
     const int br = r / 7, kr = r % 7;
     double s = 0.0;
     for (int e = 0; e < E; e++) {

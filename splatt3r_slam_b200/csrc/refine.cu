@@ -172,22 +172,23 @@ extern "C" int b200slam_refine_matches_f16(const void *D11, const void *D21, con
   cudaStream_t st = (cudaStream_t)stream;
   const __half *a = (const __half *)D11, *q = (const __half *)D21;
   const bool aligned = ((uintptr_t)D11 % 16 == 0) && ((uintptr_t)D21 % 16 == 0);
-  // Tiled kernel with bulk-copy staged windows: queries form the (h, w) pixel grid of view 2
+  // Tiled kernels with bulk-copy staged windows: queries form the (h, w) pixel grid of view 2
   // (n == h*w, as in matching.py:79-85), radius 3, and the nominal box of the coarsest level fits.
   const int reach = radius * dilation_max;
-  const long long nominal = (long long)(rtile::TW + 2 * reach + 2) * (rtile::TH + 2 * reach + 2) * fdim * 2;
-  if (fdim == 24 && aligned && radius == 3 && n == h * w && dilation_max >= 1 && nominal <= rtile::BOX_BYTES &&
-      w >= rtile::TW + 2 * reach + 2) {
-    static bool attr_set = false;
-    if (!attr_set) {
-      cudaFuncSetAttribute(rtile::refine_tile_kernel<24, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                           rtile::BOX_BYTES);
-      attr_set = true;
-    }
+  if (fdim == 24 && aligned && radius == 3 && n == h * w && dilation_max >= 1 && w >= rtile::TW + 2 * reach + 2) {
     const int tiles = ((w + rtile::TW - 1) / rtile::TW) * ((h + rtile::TH - 1) / rtile::TH);
-    rtile::refine_tile_kernel<24, 3><<<dim3(tiles, b), rtile::THREADS, rtile::BOX_BYTES, st>>>(
-        a, q, p1, p1_new, h, w, n, w, dilation_max);
-    return (int)cudaGetLastError();
+    const long long nominal = (long long)(rtile::TW + 2 * reach + 2) * (rtile::TH + 2 * reach + 2) * fdim * 2;
+    if (nominal <= rtile::BOX_BYTES) {
+      static bool attr_set = false;
+      if (!attr_set) {
+        cudaFuncSetAttribute(rtile::refine_tile_kernel<24, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             rtile::BOX_BYTES);
+        attr_set = true;
+      }
+      rtile::refine_tile_kernel<24, 3><<<dim3(tiles, b), rtile::THREADS, rtile::BOX_BYTES, st>>>(
+          a, q, p1, p1_new, h, w, n, w, dilation_max);
+      return (int)cudaGetLastError();
+    }
   }
   if (fdim == 24 && aligned)
     refine_f16_kernel<24><<<grid, RF_THREADS, 0, st>>>(a, q, p1, p1_new, h, w, n, radius, dilation_max);

@@ -99,6 +99,9 @@ def full(_):
 
 
 tb = timeit(build, 1, 10)
+tf = timeit(full, 1, 5)
 out[f"graph_N{N}_E{E}"] = {"build_us": tb, "build_GBps": E * (45.0 * n + 840) / tb / 1e3,
-                           "solve_us": timeit(solve, 1, 10), "gn_10it_us": timeit(full, 1, 5)}
+                           "gn_10it_us": tf, "solve_us": timeit(solve, 1, 10)}
+stg = wsg[:48].cpu().view(torch.int64)[2:6].tolist()
+out[f"graph_N{N}_E{E}"]["solve_kernel_ns"] = {"load": stg[1] - stg[0], "cholesky": stg[2] - stg[1], "finish": stg[3] - stg[2]}
 print(json.dumps(out))
