@@ -101,10 +101,10 @@ inline int launch_solve(float *Twc, const int64_t *ii_row, const int64_t *jj_row
   int rc = (int)cudaGetLastError();
   if (rc) return rc;
   if (D <= PACKED_MAX_D) {
-    const size_t smem = (size_t)(2 * Dp + (size_t)D * (D + 1) / 2) * sizeof(double);
+    const size_t smem = solve_smem_bytes(D, Dp, true);
     static bool attr_set = false;
     if (!attr_set) {
-      cudaFuncSetAttribute(solve_retract_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+      cudaFuncSetAttribute(solve_retract_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
       attr_set = true;
     }
     solve_retract_kernel<true><<<1, SOLVE_THREADS, smem, st>>>(Twc, A, rhs, N, D, Dp, delta_thresh, dx, state);

@@ -209,7 +209,8 @@ struct FullLower {
 // backward substitution is done by warp 0 alone with warp-level synchronisation (D <= 256).
 constexpr int CHOL_UNROLL = 7;  // register-blocked trailing update for D <= 224
 template <class Mat, bool WARP = false>
-__device__ bool cholesky_solve(Mat L, int D, double *x, double *col, int *fail) {
+__device__ bool cholesky_solve(Mat L, int D, double *x, double *col, int *fail,
+                               unsigned long long *stamp = nullptr) {
 #define CHOL_SYNC() do { if (WARP) __syncwarp(); else __syncthreads(); } while (0)
   const int tid = threadIdx.x, T = WARP ? 32 : blockDim.x;
   const int lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
@@ -268,6 +269,7 @@ __device__ bool cholesky_solve(Mat L, int D, double *x, double *col, int *fail) 
     }
     CHOL_SYNC();
   }
+  if (stamp && tid == 0) *stamp = gtimer();
   // backward: L^T x = y
   if (WARP || D <= 256) {
     if (warp == 0) {
@@ -318,10 +320,21 @@ __device__ inline void finish_update(bool ok, const double *x, double *scratch, 
   }
 }
 
-constexpr int SOLVE_THREADS = 1024;
+}  // namespace b200gn
+#include "gn_chol_blocked.cuh"
+namespace b200gn {
+
+constexpr int SOLVE_THREADS = 512;
 constexpr int PACKED_MAX_D = 217;  // 217*218/2*8 = 189 KB of packed lower triangle in smem
 
-// dynamic smem: [x: Dp][col: Dp][packed L: D(D+1)/2 if PACKED]
+// dynamic smem: [x: Dp][col: Dp][packed L: D(D+1)/2][Pt: CB*ldp][Dg: CB*CB + CB] if PACKED, else [x][col]
+__host__ __device__ inline int chol_ldp(int D) { return ((D + 3) & ~3) + 4; }
+inline size_t solve_smem_bytes(int D, int Dp, bool packed) {
+  size_t n = (size_t)2 * Dp;
+  if (packed) n += (size_t)D * (D + 1) / 2 + (size_t)CB * chol_ldp(D) + CB * CB + CB;
+  return n * sizeof(double);
+}
+
 template <bool PACKED>
 __global__ void __launch_bounds__(SOLVE_THREADS)
 solve_retract_kernel(float *__restrict__ Twc, double *__restrict__ A, const double *__restrict__ rhs,
@@ -335,15 +348,17 @@ solve_retract_kernel(float *__restrict__ Twc, double *__restrict__ A, const doub
   for (int i = tid; i < D; i += blockDim.x) x[i] = rhs[i];
   bool ok;
   if (PACKED) {
-    PackedLower L{sm + 2 * Dp};
+    double *Lp = sm + 2 * Dp;
     // one thread per element of the lower triangle (flat index -> (i,k)), coalesced along rows
     for (int t = tid; t < D * D; t += blockDim.x) {
       const int i = t / D, k = t - i * D;
-      if (k <= i) L.at(i, k) = A[t];
+      if (k <= i) Lp[(size_t)i * (i + 1) / 2 + k] = A[t];
     }
     __syncthreads();
     if (tid == 0) state->t[1] = gtimer();
-    ok = cholesky_solve(L, D, x, col, &fail);
+    double *Pt = Lp + (size_t)D * (D + 1) / 2;
+    const int ldp = chol_ldp(D);
+    ok = cholesky_blocked(Lp, D, x, Pt, ldp, Pt + (size_t)CB * ldp, &fail);
     if (tid == 0) state->t[2] = gtimer();
   } else {
     FullLower L{A, D};
