@@ -71,7 +71,7 @@ __device__ __forceinline__ bool chol_panel(double *__restrict__ Lp, int D, doubl
     }
   }
   __syncthreads();
-if (*fail) return false;
+  if (*fail) return false;
   // ---- step 2: rows below the block ---------------------------------------------------------------
   for (int i = R0 + tid; i < D; i += T) {
     double *rp = Lp + tri(i) + j0;
