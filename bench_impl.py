@@ -142,12 +142,17 @@ def run_tracker(args):
                    "l2": f"{n_sets} rotating input sets of ~56 MB (> 126 MB L2)", "ranks": "independent pairs per rank, no collective"},
         "e2e": {"value": world * N_PIX * args.steps / (ms_e2e * 1e-3), "unit": "px/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps},
-        "gpu_launches": args.steps * (2 + 4 * GN["iters"]),
+        # per step: repack_planar + iter_proj + refine_tile + first_occurrence + rank + ONE persistent GN kernel
+        # (all 10 iterations; cooperative launch) = 6 launches of this library's kernels
+        "gpu_launches": args.steps * 6,
         "kernel_us": {k: round(v, 2) for k, v in kt.items()},
         "match_px_per_s": N_PIX / ((kt["iter_proj"] + kt["refine"]) * 1e-6),
         "gn_iters_per_s": {"E2": GN["iters"] / (kt["gn"] * 1e-6)},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": roof[dom], "peak": peak, "unit": "GB/s",
                      "frac": roof[dom] / peak, "traffic": None, "peak_source": peak_src,
+                     "note": "algorithmic HBM bytes / CUDA-event time per call; refine is bound by the shared-memory pipe and the "
+                             "b=1 iter_proj / tracker GN by latency (DESIGN.md section 5); the HBM-bound kernel of this path is the "
+                             "graph-sized GN build (bench.py --workload graph)",
                      "all_kernels_GBps": {k: round(v, 1) for k, v in roof.items()}},
         "clocks": sampler.result(),
     }
