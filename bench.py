@@ -24,6 +24,10 @@ import sys
 import threading
 import time
 
+# NCCL prints its version banner on stdout at VERSION level; the contract is ONE JSON line on stdout
+if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+    os.environ["NCCL_DEBUG"] = "WARN"
+
 import torch
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
