@@ -23,6 +23,8 @@ struct State {  // head of the workspace
   unsigned ticket;  // arrival counter of the fused small-problem path (reset by the last CTA)
   unsigned long long t[4];  // %globaltimer stamps of the last fused tail: start, finalized, solved, end
   unsigned gen;  // grid-barrier generation of the persistent kernel (= iterations completed)
+  int cg_iters;        // PCG iterations of the last large-graph solve
+  double cg_rel;       // its final r^T M^-1 r relative to the initial value
 };
 __device__ __forceinline__ unsigned long long gtimer() {
   unsigned long long t;
@@ -34,7 +36,7 @@ constexpr size_t STATE_BYTES = 256;
 __host__ __device__ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Layout {
-  size_t partials, edge_blocks, A, rhs, rows, first, total;
+  size_t partials, edge_blocks, A, dense_ctrl, pcg, rhs, rows, first, total;
 };
 
 // Number of CTAs (S) that split the n points of one edge when `Ecount` edges are built by one
@@ -78,7 +80,18 @@ inline Layout make_layout(int N, int E, int n) {
   // capacity in (edge, split) slots; splits_for() clamps S so that any shard of the E edges fits
   L.partials = off; off = align256(off + partial_slots(E) * NACC * sizeof(double));
   L.edge_blocks = off; off = align256(off + (size_t)E * 56 * sizeof(double));
-  L.A = off; off = align256(off + D * D * sizeof(double));
+  // stage-3 scratch: the dense matrix (single-CTA solver for D <= 217; above that the multi-CTA tiled
+  // solver, which also needs a 256-byte control block and the inverted diagonal tiles), and the
+  // buffers of the optional PCG solver
+  // [ctrl 256 B | cnt M | ptr M+1 | list 2E (ints) | Minv 49M | b,x,r,p 4*7M | partials 4*148 (doubles)]
+  L.A = off;
+  off = align256(off + D * D * sizeof(double));
+  L.dense_ctrl = off;
+  if (D > 217) off = align256(off + 256 + ((D + 63) / 64) * 64 * 64 * sizeof(double));
+  L.pcg = off;
+  if (D > 217)
+    off = align256(off + 256 + align256((2 * (D / 7) + 2 + 2 * (size_t)E) * sizeof(int)) +
+                   (49 * (D / 7) + 4 * D + 4 * 148) * sizeof(double));
   L.rhs = off; off = align256(off + D * sizeof(double));
   L.rows = off; off = align256(off + (size_t)2 * E * sizeof(int64_t));
   L.first = off; off = align256(off + (size_t)2 * E);
@@ -254,4 +267,6 @@ __global__ void export_blocks_kernel(const double *__restrict__ edge_blocks, int
 }  // namespace b200gn
 
 #include "gn_persistent.cuh"
+#include "gn_pcg.cuh"
+#include "gn_dense.cuh"
 #include "gn_api.cuh"

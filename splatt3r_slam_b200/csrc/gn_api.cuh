@@ -91,33 +91,101 @@ inline int launch_edge_blocks(const b200slam_gn_params *p, const BuildConsts &C,
   return rc;
 }
 
+// Large graphs: block-Jacobi PCG on the edge blocks (gn_pcg.cuh), one cooperative launch.
+inline int launch_pcg(float *Twc, const int64_t *ii_row, const int64_t *jj_row, const double *edge_blocks, int N,
+                      int E, float delta_thresh, float *dx, char *ws, const Layout &L, cudaStream_t st) {
+  State *state = reinterpret_cast<State *>(ws);
+  const int M = N - NUM_FIX, D = 7 * M;
+  char *base = ws + L.pcg;
+  int rc = (int)cudaMemsetAsync(base, 0, 256, st);  // barrier counters + failure flag
+  if (rc) return rc;
+  PcgBufs B;
+  B.bar = reinterpret_cast<unsigned *>(base);
+  B.flag = reinterpret_cast<int *>(base + 64);
+  int *ints = reinterpret_cast<int *>(base + 256);
+  int *cnt = ints;
+  B.adj_ptr = ints + M;
+  B.adj_list = ints + 2 * M + 1;
+  double *dbl = reinterpret_cast<double *>(base + 256 + align256((2 * (size_t)M + 2 + 2 * (size_t)E) * sizeof(int)));
+  B.Minv = dbl;
+  B.b = dbl + (size_t)49 * M;
+  B.x = B.b + D;
+  B.r = B.x + D;
+  B.p = B.r + D;
+  B.part = B.p + D;
+  const int tb = 128, nb = (M + tb - 1) / tb;
+  adj_count_kernel<<<nb, tb, 0, st>>>(ii_row, jj_row, E, M, cnt);
+  adj_scan_kernel<<<1, 32, 0, st>>>(cnt, M, B.adj_ptr);
+  adj_fill_kernel<<<nb, tb, 0, st>>>(ii_row, jj_row, E, M, B.adj_ptr, B.adj_list);
+  rc = (int)cudaGetLastError();
+  if (rc) return rc;
+  static int num_sms = 0;
+  if (num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+  }
+  int grid = (M + PCG_WARPS - 1) / PCG_WARPS;
+  if (grid > num_sms) grid = num_sms;
+  if (grid > PCG_MAX_CTAS) grid = PCG_MAX_CTAS;
+  int max_cg = 20 * M < 4000 ? 20 * M : 4000;
+  double tol2 = 1e-26;  // (1e-13)^2 on r^T M^-1 r relative to its initial value
+  void *args[] = {&Twc, &ii_row, &jj_row, &edge_blocks, &N, &E, &B, &delta_thresh, &dx, &state, &max_cg, &tol2};
+  return (int)cudaLaunchCooperativeKernel((const void *)pcg_solve_retract_kernel, dim3(grid), dim3(PCG_THREADS), args, 0,
+                                          st);
+}
+
+// Graphs beyond the single-CTA solver: exact tiled Cholesky on all SMs (gn_dense.cuh), one cooperative launch.
+inline int launch_dense(float *Twc, const int64_t *ii_row, const int64_t *jj_row, const double *edge_blocks, int N,
+                        int E, float delta_thresh, float *dx, char *ws, const Layout &L, cudaStream_t st) {
+  State *state = reinterpret_cast<State *>(ws);
+  int M = N - NUM_FIX, D = 7 * M;
+  DenseBufs B;
+  B.A = reinterpret_cast<double *>(ws + L.A);
+  B.b = reinterpret_cast<double *>(ws + L.rhs);
+  B.bar = reinterpret_cast<unsigned *>(ws + L.dense_ctrl);
+  B.flag = reinterpret_cast<int *>(ws + L.dense_ctrl + 64);
+  B.W = reinterpret_cast<double *>(ws + L.dense_ctrl + 256);
+  int rc = (int)cudaMemsetAsync(ws + L.dense_ctrl, 0, 256, st);
+  if (rc) return rc;
+  assemble_kernel<<<M, 256, 0, st>>>(ii_row, jj_row, edge_blocks, E, D, B.A, B.b, state);
+  rc = (int)cudaGetLastError();
+  if (rc) return rc;
+  static int num_sms = 0;
+  const size_t smem = (size_t)DENSE_SMEM_DOUBLES * sizeof(double);
+  if (num_sms == 0) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaFuncSetAttribute(dense_solve_retract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  }
+  void *args[] = {&Twc, &B, &N, &D, &delta_thresh, &dx, &state};
+  return (int)cudaLaunchCooperativeKernel((const void *)dense_solve_retract_kernel, dim3(num_sms), dim3(DENSE_THREADS),
+                                          args, smem, st);
+}
+
 inline int launch_solve(float *Twc, const int64_t *ii_row, const int64_t *jj_row,
                         const double *edge_blocks, int N, int E, float delta_thresh, float *dx, char *ws,
                         const Layout &L, cudaStream_t st) {
   State *state = reinterpret_cast<State *>(ws);
-  double *A = reinterpret_cast<double *>(ws + L.A), *rhs = reinterpret_cast<double *>(ws + L.rhs);
   const int M = N - NUM_FIX, D = 7 * M, Dp = D < 32 ? 32 : D;
+  if (D > PACKED_MAX_D) {
+    // exact tiled Cholesky by default; B200SLAM_GN_PCG=1 selects the matrix-free PCG (well-connected huge graphs)
+    static const bool use_pcg = getenv("B200SLAM_GN_PCG") != nullptr;
+    return use_pcg ? launch_pcg(Twc, ii_row, jj_row, edge_blocks, N, E, delta_thresh, dx, ws, L, st)
+                   : launch_dense(Twc, ii_row, jj_row, edge_blocks, N, E, delta_thresh, dx, ws, L, st);
+  }
+  double *A = reinterpret_cast<double *>(ws + L.A), *rhs = reinterpret_cast<double *>(ws + L.rhs);
   assemble_kernel<<<M, 256, 0, st>>>(ii_row, jj_row, edge_blocks, E, D, A, rhs, state);
   int rc = (int)cudaGetLastError();
   if (rc) return rc;
-  if (D <= PACKED_MAX_D) {
-    const size_t smem = solve_smem_bytes(D, Dp, true);
-    static bool attr_set = false;
-    if (!attr_set) {
-      cudaFuncSetAttribute(solve_retract_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-      attr_set = true;
-    }
-    solve_retract_kernel<true><<<1, SOLVE_THREADS, smem, st>>>(Twc, A, rhs, N, D, Dp, delta_thresh, dx, state);
-  } else {
-    const size_t smem = (size_t)2 * Dp * sizeof(double);
-    if (smem > 200 * 1024) return B200SLAM_EINVAL;
-    static bool attr_set2 = false;
-    if (!attr_set2) {
-      cudaFuncSetAttribute(solve_retract_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
-      attr_set2 = true;
-    }
-    solve_retract_kernel<false><<<1, SOLVE_THREADS, smem, st>>>(Twc, A, rhs, N, D, Dp, delta_thresh, dx, state);
+  const size_t smem = solve_smem_bytes(D, Dp, true);
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(solve_retract_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    attr_set = true;
   }
+  solve_retract_kernel<true><<<1, SOLVE_THREADS, smem, st>>>(Twc, A, rhs, N, D, Dp, delta_thresh, dx, state);
   return (int)cudaGetLastError();
 }
 

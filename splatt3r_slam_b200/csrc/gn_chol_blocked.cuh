@@ -31,42 +31,44 @@ __device__ __forceinline__ bool chol_panel(double *__restrict__ Lp, int D, doubl
                                            double *__restrict__ yv, int *fail, int j0, int nb_rt) {
   const int tid = threadIdx.x, T = blockDim.x, lane = tid & 31, warp = tid >> 5, nwarp = T >> 5;
   const int nb = FULL ? CB : nb_rt, R0 = j0 + nb;  // FULL: compile-time width => straight-line, batched loads
-  // ---- step 1: diagonal block (+ rhs) by warp 0 ---------------------------------------------------
-  if (warp == 0) {
-    double row[CB];
+  // ---- step 1: diagonal block (+ rhs) by ONE thread, fully unrolled in registers -------------------
+  // (a shuffle-based warp version measured ~5 k cycles per panel: 64-bit shuffles + rsqrt chains)
+  if (tid == 0) {
+    double a[CB][CB], y[CB];
 #pragma unroll
-    for (int c = 0; c < CB; c++) {
-      double v = 0.0;
-      if (lane < nb && c <= lane) v = Lp[tri(j0 + lane) + j0 + c];
-      if (lane == CB && c < nb) v = x[j0 + c];
-      row[c] = v;
+    for (int r = 0; r < CB; r++) {
+#pragma unroll
+      for (int c = 0; c <= r; c++) a[r][c] = r < nb ? Lp[tri(j0 + r) + j0 + c] : (r == c ? 1.0 : 0.0);
+      y[r] = r < nb ? x[j0 + r] : 0.0;
     }
     bool bad = false;
 #pragma unroll
     for (int c = 0; c < CB; c++) {
-      if (c < nb) {  // uniform
-        const double d = shfl_d(row[c], c);
-        if (!(d > 0.0)) bad = true;
-        const double dinv = rsqrt(d);
-        const double l = row[c] * dinv;
-        row[c] = lane == c ? dinv : l;
+      const double d = a[c][c];
+      if (!(d > 0.0)) bad = true;
+      const double dinv = rsqrt(d);
+      a[c][c] = dinv;
+      y[c] *= dinv;
 #pragma unroll
-        for (int c2 = c + 1; c2 < CB; c2++) {
-          const double lc2 = shfl_d(l, c2);  // L(c2, c)
-          if (c2 < nb) row[c2] -= l * lc2;
-        }
+      for (int r = c + 1; r < CB; r++) a[r][c] *= dinv;
+#pragma unroll
+      for (int r = c + 1; r < CB; r++) {
+#pragma unroll
+        for (int c2 = c + 1; c2 <= r; c2++) a[r][c2] -= a[r][c] * a[c2][c];
+        y[r] -= a[r][c] * y[c];
       }
     }
-    if (bad && lane == 0) *fail = 1;
+    if (bad) *fail = 1;
 #pragma unroll
-    for (int c = 0; c < CB; c++) {
-      if (lane < nb && c <= lane) {
-        Lp[tri(j0 + lane) + j0 + c] = row[c];
-        Dg[lane * CB + c] = row[c];
-      }
-      if (lane == CB && c < nb) {
-        x[j0 + c] = row[c];
-        yv[c] = row[c];
+    for (int r = 0; r < CB; r++) {
+      if (r < nb) {
+#pragma unroll
+        for (int c = 0; c <= r; c++) {
+          Lp[tri(j0 + r) + j0 + c] = a[r][c];
+          Dg[r * CB + c] = a[r][c];
+        }
+        x[j0 + r] = y[r];
+        yv[r] = y[r];
       }
     }
   }
@@ -166,7 +168,8 @@ __device__ __forceinline__ void chol_back_panel(const double *__restrict__ Lp, d
 
 // Lp: packed lower triangle; x: rhs in / solution out; Pt: CB * ldp doubles; Dg: CB*CB + CB doubles.
 __device__ inline bool cholesky_blocked(double *__restrict__ Lp, int D, double *__restrict__ x,
-                                        double *__restrict__ Pt, int ldp, double *__restrict__ Dg, int *fail) {
+                                        double *__restrict__ Pt, int ldp, double *__restrict__ Dg, int *fail,
+                                        bool do_back = true) {
   double *yv = Dg + CB * CB;
   if (threadIdx.x == 0) *fail = 0;
   __syncthreads();
@@ -176,6 +179,7 @@ __device__ inline bool cholesky_blocked(double *__restrict__ Lp, int D, double *
                              : chol_panel<false>(Lp, D, x, Pt, ldp, Dg, yv, fail, j0, nb);
     if (!ok) return false;
   }
+  if (!do_back) return true;  // caller wants L (reciprocal diagonal) and y = L^-1 b only
   // backward substitution L^T x = y, panel by panel from the bottom
   for (int j0 = ((D - 1) / CB) * CB; j0 >= 0; j0 -= CB) {
     const int nb = min(CB, D - j0);
