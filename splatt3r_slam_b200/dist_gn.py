@@ -102,12 +102,12 @@ def bench_graph(args, rank, world, local):
     from . import synthetic
     dev = torch.device("cuda", local)
     N, E = args.kfs, args.edges
-    g = synthetic.make_graph(seed=7, N=N, E_undirected=E // 2, h=384, w=512)
-    n = g["Xs"].shape[1]
+    n = 384 * 512
     e0, Ec = shard_range(E, rank, world)
-    sl = slice(e0, e0 + Ec)
-    G = {k: g[k].to(dev) for k in ("Twc", "Xs", "Cs", "ii", "jj")}
-    idx_s, val_s, Q_s = g["idx_ii2jj"][sl].to(dev), g["valid_match"][sl].to(dev), g["Q"][sl].to(dev)
+    # generated on the device, this rank's edge shard only (configs[3] is 21 GB of per-edge arrays)
+    g = synthetic.make_graph_device(7, N, E // 2, 384, 512, dev, edge_range=(e0, e0 + Ec))
+    G = {k: g[k] for k in ("Twc", "Xs", "Cs", "ii", "jj")}
+    idx_s, val_s, Q_s = g["idx_ii2jj"], g["valid_match"], g["Q"]
     prm = be.make_params(0, 0.003, 10.0, 0.0, 1.5)
     rows = be.edge_rows(G["ii"], G["jj"])
     hooks = CudaHooks(prm, N, E, n, dev)

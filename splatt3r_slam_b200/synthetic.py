@@ -34,7 +34,7 @@ def sim3_act(T, X):
 
 
 def sim3_inv_act(T, X):
-    q = T[..., 3:7] * torch.tensor([-1.0, -1.0, -1.0, 1.0], dtype=T.dtype)
+    q = T[..., 3:7] * torch.tensor([-1.0, -1.0, -1.0, 1.0], dtype=T.dtype, device=T.device)
     return quat_rotate(q, X - T[..., 0:3]) / T[..., 7:8]
 
 
@@ -67,12 +67,13 @@ class Scene:
     def raycast(self, T):
         """World points (h,w,3) hit by the pixel rays of the camera at Sim3 pose T (fp64)."""
         h, w, K = self.h, self.w, self.K
-        v, u = torch.meshgrid(torch.arange(h, dtype=torch.float64), torch.arange(w, dtype=torch.float64),
+        dev = K.device
+        v, u = torch.meshgrid(torch.arange(h, dtype=torch.float64, device=dev), torch.arange(w, dtype=torch.float64, device=dev),
                               indexing="ij")
         d_cam = torch.stack([(u - K[0, 2]) / K[0, 0], (v - K[1, 2]) / K[1, 1], torch.ones_like(u)], -1)
         d = quat_rotate(T[3:7], d_cam)  # world direction (scale folded into the ray parameter)
         o = T[0:3]
-        t = torch.full((h, w), 2.0, dtype=torch.float64)
+        t = torch.full((h, w), 2.0, dtype=torch.float64, device=dev)
         for _ in range(8):
             P = o + t[..., None] * d
             t = t + (self.surf(P[..., 0], P[..., 1]) - P[..., 2]) / d[..., 2]
@@ -166,3 +167,66 @@ def make_graph(seed=0, N=2, E_undirected=1, h=384, w=512, noise=0.001, pose_nois
                 Cs=Cs.float().contiguous(), K=sc.K.float().contiguous(), ii=ii, jj=jj,
                 idx_ii2jj=idx.contiguous(), valid_match=valid.contiguous(),
                 Q=Q.float().contiguous(), h=h, w=w)
+
+
+def make_graph_device(seed, N, E_undirected, h, w, device, edge_range=None, noise=0.001, pose_noise=0.01):
+    """Same construction as make_graph, for graphs too large to build on the host (BASELINE configs[3]:
+    N = 1024, E = 8192 at 512x384 is 21 GB of per-edge arrays): topology and poses come from the CPU
+    generator (identical on every rank), the pointmaps / confidences / per-edge arrays are generated ON
+    `device` with a device generator, and only the directed edges [e0, e1) of `edge_range` are
+    materialised (a rank's shard).  Values differ from make_graph's for the same seed (different random
+    streams); statistics and structure are the same."""
+    sc = Scene(seed, h, w)
+    g = sc.gen
+    n = h * w
+    poses = [torch.tensor([0, 0, 0, 0, 0, 0, 1, 1], dtype=torch.float64)]
+    for k in range(1, N):
+        poses.append(random_pose(g, rot_deg=6.0, trans=0.15, scale=0.05))
+    Tgt = torch.stack(poses)
+    und = [(k, (k + 1) % N) for k in range(min(N - 1 if N == 2 else N, E_undirected))]
+    while len(und) < E_undirected:
+        a, b_ = torch.randint(0, N, (2,), generator=g).tolist()
+        if a != b_:
+            und.append((a, b_))
+    ii = torch.tensor([a for a, _ in und] + [b_ for _, b_ in und], dtype=torch.int64)
+    jj = torch.tensor([b_ for _, b_ in und] + [a for a, _ in und], dtype=torch.int64)
+    E = ii.numel()
+    T = Tgt.clone()
+    for k in range(1, N):
+        d = random_pose(g, rot_deg=math.degrees(pose_noise), trans=pose_noise, scale=pose_noise)
+        t = d[7] * quat_rotate(d[3:7], T[k, 0:3]) + d[0:3]
+        qd, q = d[3:7], T[k, 3:7]
+        qn = torch.stack([
+            qd[3] * q[0] + qd[0] * q[3] + qd[1] * q[2] - qd[2] * q[1],
+            qd[3] * q[1] - qd[0] * q[2] + qd[1] * q[3] + qd[2] * q[0],
+            qd[3] * q[2] + qd[0] * q[1] - qd[1] * q[0] + qd[2] * q[3],
+            qd[3] * q[3] - qd[0] * q[0] - qd[1] * q[1] - qd[2] * q[2]])
+        T[k] = torch.cat([t, qn, (d[7] * T[k, 7]).reshape(1)])
+    # heavy arrays on the device
+    sc.K, sc.freq, sc.phase = sc.K.to(device), sc.freq.to(device), sc.phase.to(device)
+    dg = torch.Generator(device=device).manual_seed(seed * 7919 + 13)
+    Tg = Tgt.to(device)
+    Xs = torch.empty((N, n, 3), dtype=torch.float32, device=device)
+    Cs = torch.empty((N, n, 1), dtype=torch.float32, device=device)
+    for k in range(N):
+        Pw = sc.raycast(Tg[k])
+        X = sim3_inv_act(Tg[k], Pw).reshape(n, 3)
+        Xs[k] = (X + noise * torch.randn(n, 3, generator=dg, dtype=torch.float64, device=device)).float()
+        Cs[k] = (1.0 + torch.exp(0.5 * torch.randn(n, 1, generator=dg, dtype=torch.float32, device=device)))
+    e0, e1 = (0, E) if edge_range is None else edge_range
+    Ec = e1 - e0
+    idx = torch.zeros((Ec, n), dtype=torch.int64, device=device)
+    valid = torch.zeros((Ec, n, 1), dtype=torch.bool, device=device)
+    Q = torch.empty((Ec, n, 1), dtype=torch.float32, device=device)
+    for e in range(e0, e1):
+        i, j = int(ii[e]), int(jj[e])
+        Pw_j = sim3_act(Tg[j], Xs[j].double())  # world points of keyframe j (noise included: sub-pixel)
+        u, v, z = sc.project(Tg[i], Pw_j)
+        ui, vi = torch.round(u).long(), torch.round(v).long()
+        ok = (ui >= 0) & (ui < w) & (vi >= 0) & (vi < h) & (z > 0)
+        idx[e - e0] = torch.where(ok, ui.clamp(0, w - 1) + w * vi.clamp(0, h - 1), torch.zeros_like(ui))
+        valid[e - e0, :, 0] = ok
+        eg = torch.Generator(device=device).manual_seed(seed * 104729 + e)  # per edge: independent of the sharding
+        Q[e - e0] = 1.0 + torch.exp(0.5 * torch.randn(n, 1, generator=eg, dtype=torch.float32, device=device))
+    return dict(Twc=T.float().contiguous().to(device), Twc_gt=Tgt.float(), Xs=Xs, Cs=Cs, K=sc.K.float().contiguous(),
+                ii=ii.to(device), jj=jj.to(device), idx_ii2jj=idx, valid_match=valid, Q=Q, h=h, w=w)
