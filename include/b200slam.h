@@ -52,6 +52,23 @@ int b200slam_refine_matches_f32(const float *D11, const float *D21, const int64_
                                 int64_t *p1_new, int b, int h, int w, int n, int fdim, int radius,
                                 int dilation_max, void *stream);
 
+/* Fused match_iterative_proj: replaces the PyTorch glue of splatt3r_slam/matching.py:25-49
+ * (prep_for_iter_proj: F.normalize, image.py:5-38 gradients, cat/permute, lin_to_pixel), :52-65
+ * (iter_proj call), :66-76 (occlusion distance test), :78-85 (refine_matches on .half() descriptors)
+ * and :87-90 (pixel_to_lin) by four kernel launches.  NOT an entry of the reference module: the
+ * reference's matching.py would call it instead of its own glue.
+ * X11, X21 (b,h,w,3) f32 pointmaps; D11, D21 (b,h,w,fdim) descriptors, f16 (desc_f32 = 0) or f32
+ * (desc_f32 = 1: rounded to f16 first, as `.half()` does); idx_init (b,h*w) i64 or NULL (identity map)
+ * -> idx_1_to_2 (b,h*w) i64 linear index u + w*v; valid (b,h*w) u8 = converged & (distance < dist_thresh).
+ * radius == 0 skips the descriptor refinement (matching.py:78).  Same float operation order as
+ * torch's CUDA kernels for that glue, so results equal the unfused path bit for bit. */
+size_t b200slam_match_workspace_bytes(int b, int h, int w, int fdim, int desc_f32);
+int b200slam_match(const float *X11, const float *X21, const void *D11, const void *D21,
+                   int desc_f32, const int64_t *idx_init, int64_t *idx_1_to_2, uint8_t *valid,
+                   int b, int h, int w, int fdim, int max_iter, float lambda_init, float cost_thresh,
+                   float dist_thresh, int radius, int dilation_max, void *workspace,
+                   size_t workspace_bytes, void *stream);
+
 /* Scalar parameters of the three GN residual models (union of the reference's scalar args,
  * gn.h:22-117).  sigma_a/sigma_b: rays = (sigma_ray, sigma_dist); calib = (sigma_pixel,
  * sigma_depth); points = (sigma_point, unused). */

@@ -44,24 +44,11 @@ __device__ __forceinline__ Resid residual(float c0, float c1, float c2, float p0
   return r;
 }
 
-// One thread per query pixel; planes (9, h*w) of batch row blockIdx.y.
-__global__ void __launch_bounds__(IP_THREADS)
-iter_proj_kernel(const float *__restrict__ planes, const float *__restrict__ pts,
-                 const float *__restrict__ p_init, float *__restrict__ p_new,
-                 uint8_t *__restrict__ converged, int h, int w, int n, int max_iter,
-                 float lambda_init, float cost_thresh) {
-  const int q = blockIdx.x * IP_THREADS + threadIdx.x;
-  if (q >= n) return;
-  const size_t bq = (size_t)blockIdx.y * n + q;
-  const int hw = h * w;
-  const float *img = planes + (size_t)blockIdx.y * hw * 9;
-
-  const float2 pi = __ldg(reinterpret_cast<const float2 *>(p_init) + bq);
-  const float umax = (float)(w - 2), vmax = (float)(h - 2);
-  float u = clampf(pi.x, 1.0f, umax);
-  float v = clampf(pi.y, 1.0f, vmax);
-  const float p0 = __ldg(pts + bq * 3 + 0), p1 = __ldg(pts + bq * 3 + 1), p2 = __ldg(pts + bq * 3 + 2);
-
+// LM loop of one query: img = the 9 planes of its batch row, (u, v) = clamped start pixel (in/out),
+// (p0, p1, p2) = target ray.  Returns the converged flag.
+__device__ __forceinline__ bool iter_proj_core(const float *__restrict__ img, int hw, int w, float umax, float vmax,
+                                               float &u, float &v, float p0, float p1, float p2, int max_iter,
+                                               float lambda_init, float cost_thresh) {
   float lambda = lambda_init;
   bool conv = false;
   if (max_iter > 0) {
@@ -125,6 +112,27 @@ iter_proj_kernel(const float *__restrict__ planes, const float *__restrict__ pts
       }
     }
   }
+  return conv;
+}
+
+// One thread per query pixel; planes (9, h*w) of batch row blockIdx.y.
+__global__ void __launch_bounds__(IP_THREADS)
+iter_proj_kernel(const float *__restrict__ planes, const float *__restrict__ pts,
+                 const float *__restrict__ p_init, float *__restrict__ p_new,
+                 uint8_t *__restrict__ converged, int h, int w, int n, int max_iter,
+                 float lambda_init, float cost_thresh) {
+  const int q = blockIdx.x * IP_THREADS + threadIdx.x;
+  if (q >= n) return;
+  const size_t bq = (size_t)blockIdx.y * n + q;
+  const int hw = h * w;
+  const float *img = planes + (size_t)blockIdx.y * hw * 9;
+
+  const float2 pi = __ldg(reinterpret_cast<const float2 *>(p_init) + bq);
+  const float umax = (float)(w - 2), vmax = (float)(h - 2);
+  float u = clampf(pi.x, 1.0f, umax);
+  float v = clampf(pi.y, 1.0f, vmax);
+  const float p0 = __ldg(pts + bq * 3 + 0), p1 = __ldg(pts + bq * 3 + 1), p2 = __ldg(pts + bq * 3 + 2);
+  const bool conv = iter_proj_core(img, hw, w, umax, vmax, u, v, p0, p1, p2, max_iter, lambda_init, cost_thresh);
   reinterpret_cast<float2 *>(p_new)[bq] = make_float2(u, v);
   converged[bq] = conv ? 1 : 0;
 }

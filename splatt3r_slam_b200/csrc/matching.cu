@@ -77,6 +77,7 @@ repack_planar_kernel(const float *__restrict__ rays_img, float *__restrict__ pla
 }
 
 #include "iter_proj_kernel.cuh"
+#include "match_fused.cuh"
 
 }  // namespace
 
@@ -104,5 +105,82 @@ extern "C" int b200slam_iter_proj(const float *rays_img, const float *pts_3d_nor
   dim3 grid((n + IP_THREADS - 1) / IP_THREADS, b);
   iter_proj_kernel<<<grid, IP_THREADS, 0, st>>>(planes, pts_3d_norm, p_init, p_new, converged, h, w, n,
                                                 max_iter, lambda_init, cost_thresh);
+  return (int)cudaGetLastError();
+}
+
+// ---- fused match_iterative_proj --------------------------------------------
+extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, const int64_t *p1,
+                                            int64_t *p1_new, int b, int h, int w, int n, int fdim,
+                                            int radius, int dilation_max, int lin_out, int *used_tile,
+                                            void *stream);
+
+namespace {
+struct MatchLayout {
+  size_t planes, p1, p1b, d11h, d21h, total;
+};
+MatchLayout match_layout(int b, int h, int w, int fdim, int desc_f32) {
+  const size_t hw = (size_t)h * w, al = 256;
+  auto up = [&](size_t x) { return (x + al - 1) / al * al; };
+  MatchLayout L;
+  size_t off = 0;
+  L.planes = off; off += up((size_t)b * hw * 9 * sizeof(float));
+  L.p1 = off;     off += up((size_t)b * hw * 2 * sizeof(int64_t));
+  L.p1b = off;    off += up((size_t)b * hw * 2 * sizeof(int64_t));
+  L.d11h = off;   off += desc_f32 ? up((size_t)b * hw * fdim * sizeof(__half)) : 0;
+  L.d21h = off;   off += desc_f32 ? up((size_t)b * hw * fdim * sizeof(__half)) : 0;
+  L.total = off;
+  return L;
+}
+}  // namespace
+
+extern "C" size_t b200slam_match_workspace_bytes(int b, int h, int w, int fdim, int desc_f32) {
+  if (b < 0 || h < 0 || w < 0 || fdim < 0) return 0;
+  return match_layout(b, h, w, fdim, desc_f32).total;
+}
+
+extern "C" int b200slam_match(const float *X11, const float *X21, const void *D11, const void *D21,
+                              int desc_f32, const int64_t *idx_init, int64_t *idx_1_to_2,
+                              uint8_t *valid, int b, int h, int w, int fdim, int max_iter,
+                              float lambda_init, float cost_thresh, float dist_thresh, int radius,
+                              int dilation_max, void *workspace, size_t workspace_bytes, void *stream) {
+  if (b < 0 || h < 0 || w < 0) return B200SLAM_EINVAL;
+  if (b == 0 || h == 0 || w == 0) return B200SLAM_OK;
+  if (!X11 || !X21 || !idx_1_to_2 || !valid) return B200SLAM_EINVAL;
+  if (radius > 0 && (!D11 || !D21 || fdim < 1)) return B200SLAM_EINVAL;
+  if (h < 3 || w < 3 || (long long)h * w * 9 > 0x7fffffffLL) return B200SLAM_EINVAL;
+  const MatchLayout L = match_layout(b, h, w, fdim, radius > 0 ? desc_f32 : 0);
+  if (!workspace || workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  char *ws = (char *)workspace;
+  float *planes = (float *)(ws + L.planes);
+  int64_t *p1 = (int64_t *)(ws + L.p1), *p1b = (int64_t *)(ws + L.p1b);
+  const int hw = h * w;
+  const size_t total = (size_t)b * hw;
+
+  prep_planes_kernel<<<dim3((w + PREP_TW - 1) / PREP_TW, (h + PREP_TH - 1) / PREP_TH, b), PREP_THREADS, 0, st>>>(
+      X11, planes, h, w);
+  match_proj_kernel<<<dim3((hw + IP_THREADS - 1) / IP_THREADS, b), IP_THREADS, 0, st>>>(
+      planes, X11, X21, idx_init, p1, valid, h, w, max_iter, lambda_init, cost_thresh, dist_thresh);
+  const int64_t *pairs = p1;
+  if (radius > 0) {
+    const void *a = D11, *q = D21;
+    if (desc_f32) {  // matching.py:80-81: D11.half(), D21.half()
+      const size_t nd = total * fdim;
+      const unsigned blocks = (unsigned)((nd + 1023) / 1024);
+      to_half_kernel<<<blocks, 256, 0, st>>>((const float *)D11, (__half *)(ws + L.d11h), nd);
+      to_half_kernel<<<blocks, 256, 0, st>>>((const float *)D21, (__half *)(ws + L.d21h), nd);
+      a = ws + L.d11h;
+      q = ws + L.d21h;
+    }
+    int used_tile = -1;
+    int rc = b200slam_internal_refine_f16(a, q, p1, idx_1_to_2, b, h, w, hw, fdim, radius, dilation_max, 1,
+                                          &used_tile, stream);
+    if (rc == B200SLAM_OK && used_tile == 1) return (int)cudaGetLastError();
+    if (used_tile != 0) return rc;  // a real argument error
+    rc = b200slam_internal_refine_f16(a, q, p1, p1b, b, h, w, hw, fdim, radius, dilation_max, 0, &used_tile, stream);
+    if (rc != B200SLAM_OK) return rc;
+    pairs = p1b;
+  }
+  pixel_to_lin_kernel<<<(unsigned)((total + 255) / 256), 256, 0, st>>>(pairs, idx_1_to_2, total, w);
   return (int)cudaGetLastError();
 }

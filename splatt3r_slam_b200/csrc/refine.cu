@@ -161,9 +161,12 @@ refine_f32_kernel(const float *__restrict__ D11, const float *__restrict__ D21,
 
 }  // namespace
 
-extern "C" int b200slam_refine_matches_f16(const void *D11, const void *D21, const int64_t *p1,
-                                           int64_t *p1_new, int b, int h, int w, int n, int fdim,
-                                           int radius, int dilation_max, void *stream) {
+// lin_out != 0: p1_new is (b,n) linear indices u + w*v instead of (b,n,2) pixels (tiled kernel only;
+// otherwise EINVAL and the caller converts).  *used_tile reports which path ran.
+extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, const int64_t *p1,
+                                            int64_t *p1_new, int b, int h, int w, int n, int fdim,
+                                            int radius, int dilation_max, int lin_out, int *used_tile,
+                                            void *stream) {
   if (b < 0 || n < 0) return B200SLAM_EINVAL;
   if (b == 0 || n == 0) return B200SLAM_OK;
   if (!D11 || !D21 || !p1 || !p1_new) return B200SLAM_EINVAL;
@@ -186,10 +189,13 @@ extern "C" int b200slam_refine_matches_f16(const void *D11, const void *D21, con
         attr_set = true;
       }
       rtile::refine_tile_kernel<24, 3><<<dim3(tiles, b), rtile::THREADS, rtile::BOX_BYTES, st>>>(
-          a, q, p1, p1_new, h, w, n, w, dilation_max);
+          a, q, p1, p1_new, h, w, n, w, dilation_max, lin_out);
+      if (used_tile) *used_tile = 1;
       return (int)cudaGetLastError();
     }
   }
+  if (used_tile) *used_tile = 0;
+  if (lin_out) return B200SLAM_EINVAL;  // caller converts (b200slam_match keeps a pair buffer for this case)
   if (fdim == 24 && aligned)
     refine_f16_kernel<24><<<grid, RF_THREADS, 0, st>>>(a, q, p1, p1_new, h, w, n, radius, dilation_max);
   else if (fdim == 16 && aligned)
@@ -200,6 +206,12 @@ extern "C" int b200slam_refine_matches_f16(const void *D11, const void *D21, con
     refine_f16_generic_kernel<<<grid, RF_THREADS, 0, st>>>(a, q, p1, p1_new, h, w, n, fdim, radius,
                                                            dilation_max);
   return (int)cudaGetLastError();
+}
+
+extern "C" int b200slam_refine_matches_f16(const void *D11, const void *D21, const int64_t *p1,
+                                           int64_t *p1_new, int b, int h, int w, int n, int fdim,
+                                           int radius, int dilation_max, void *stream) {
+  return b200slam_internal_refine_f16(D11, D21, p1, p1_new, b, h, w, n, fdim, radius, dilation_max, 0, nullptr, stream);
 }
 
 extern "C" int b200slam_refine_matches_f32(const float *D11, const float *D21, const int64_t *p1,

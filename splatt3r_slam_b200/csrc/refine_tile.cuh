@@ -110,7 +110,7 @@ template <int FDIM, int RADIUS>
 __global__ void __launch_bounds__(THREADS, 2)
 refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D21,
                    const int64_t *__restrict__ p1, int64_t *__restrict__ p1_new, int h, int w, int n,
-                   int qw, int dilation_max) {
+                   int qw, int dilation_max, int lin_out) {
   extern __shared__ __align__(128) unsigned char box_mem[];
   __shared__ uint64_t bar;
   __shared__ int red[THREADS / 32][6];
@@ -239,7 +239,8 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
   if (active) {
     // queries that could never hit the image keep their input pixel verbatim (64-bit)
     const longlong2 out = can_hit ? make_longlong2(u_new, v_new) : pin;
-    reinterpret_cast<longlong2 *>(p1_new)[bq] = out;
+    if (lin_out) p1_new[bq] = out.x + (long long)w * out.y;  // pixel_to_lin (matching.py:13-15) folded in
+    else reinterpret_cast<longlong2 *>(p1_new)[bq] = out;
   }
 }
 

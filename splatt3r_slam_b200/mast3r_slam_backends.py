@@ -49,9 +49,12 @@ def _load():
     lib.b200slam_gauss_newton.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_gauss_newton_ids.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_edge_rows.argtypes = [vp, vp, i, vp, vp, sz, vp]
+    lib.b200slam_match_workspace_bytes.argtypes = [i] * 5
+    lib.b200slam_match_workspace_bytes.restype = sz
+    lib.b200slam_match.argtypes = [vp] * 4 + [i] + [vp] * 3 + [i] * 5 + [f, f, f, i, i, vp, sz, vp]
     for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "gn_build_blocks",
                  "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gauss_newton",
-                 "gauss_newton_ids", "edge_rows"):
+                 "gauss_newton_ids", "edge_rows", "match"):
         getattr(lib, "b200slam_" + name).restype = i
     return lib
 
@@ -135,6 +138,40 @@ def refine_matches(D11, D21, p1, radius, dilation_max):
         _check(fn(*ptrs, p1_new.data_ptr(), b, h, w, n, fdim, int(radius), int(dilation_max), _stream(p1)),
                "refine_matches")
     return [p1_new]
+
+
+def match(X11, X21, D11, D21, idx_1_to_2_init, max_iter, lambda_init, cost_thresh, dist_thresh, radius,
+          dilation_max):
+    """Fused `match_iterative_proj` (reference matching.py:52-90 including prep_for_iter_proj :25-49
+    and the occlusion test :66-76): X11, X21 (b,h,w,3) f32; D11 (b,h,w,fdim), D21 (b,h,w,fdim) or
+    (b,h*w,fdim), f16 or f32 (f32 is rounded to f16 like the reference's `.half()`);
+    idx_1_to_2_init (b,h*w) int64 or None.  Returns [idx_1_to_2 (b,h*w) int64, valid (b,h*w,1) bool] —
+    bit-identical to the unfused glue + iter_proj + refine_matches (an entry
+    point the reference does not have; `splatt3r_slam_b200.matching.match(..., fused=True)` uses it)."""
+    _contig(X11=X11, X21=X21, D11=D11, D21=D21)
+    b, h, w, _ = X11.shape
+    fdim = D11.shape[-1]
+    if D11.dtype not in (torch.float16, torch.float32) or D21.dtype != D11.dtype:
+        raise RuntimeError(f"match: unsupported descriptor dtypes {D11.dtype}, {D21.dtype}")
+    ptrs = (_cuda(X11, torch.float32, "X11"), _cuda(X21, torch.float32, "X21"), _cuda(D11, D11.dtype, "D11"),
+            _cuda(D21, D11.dtype, "D21"))
+    f32 = int(D11.dtype == torch.float32)
+    init = None
+    if idx_1_to_2_init is not None:
+        _contig(idx_1_to_2_init=idx_1_to_2_init)
+        init = _cuda(idx_1_to_2_init, torch.int64, "idx_1_to_2_init")
+    with _guard(X11):
+        idx = torch.empty((b, h * w), dtype=torch.int64, device=X11.device)
+        valid = torch.empty((b, h * w, 1), dtype=torch.bool, device=X11.device)
+        nbytes = _lib.b200slam_match_workspace_bytes(b, h, w, fdim, f32)
+        key = ("match", X11.device.index)
+        ws = _workspaces.get(key)
+        if ws is None or ws.numel() < nbytes:
+            ws = _workspaces[key] = torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=X11.device)
+        _check(_lib.b200slam_match(*ptrs, f32, init, idx.data_ptr(), valid.data_ptr(), b, h, w, fdim, int(max_iter),
+                                   float(lambda_init), float(cost_thresh), float(dist_thresh), int(radius),
+                                   int(dilation_max), ws.data_ptr(), nbytes, _stream(X11)), "match")
+    return [idx, valid]
 
 
 def edge_rows(ii, jj):

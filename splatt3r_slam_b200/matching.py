@@ -69,5 +69,17 @@ def match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init=None, cfg=None, bac
     return pixel_to_lin(p1, w), valid_proj2.unsqueeze(-1)
 
 
-def match(X11, X21, D11, D21, idx_1_to_2_init=None, cfg=None, backend=None):
+def match_fused(X11, X21, D11, D21, idx_1_to_2_init=None, cfg=None, backend=None):
+    """Same inputs and outputs as `match_iterative_proj`, through the backend's single fused entry
+    (`b200slam_match`: 4 launches instead of ~12 torch kernels + 3 backend launches)."""
+    cfg = DEFAULT_CFG if cfg is None else cfg
+    be = _default_backend() if backend is None else backend
+    idx, valid = be.match(X11, X21, D11, D21, idx_1_to_2_init, cfg["max_iter"], cfg["lambda_init"],
+                          cfg["convergence_thresh"], cfg["dist_thresh"], cfg["radius"], cfg["dilation_max"])
+    return idx, valid
+
+
+def match(X11, X21, D11, D21, idx_1_to_2_init=None, cfg=None, backend=None, fused=False):
+    if fused:
+        return match_fused(X11, X21, D11, D21, idx_1_to_2_init, cfg, backend)
     return match_iterative_proj(X11, X21, D11, D21, idx_1_to_2_init, cfg, backend)

@@ -47,6 +47,14 @@ out["iter_proj_us"] = timeit(lambda i: be.iter_proj(sets[i]["rays"], sets[i]["pt
                                                     cfg["lambda_init"], cfg["convergence_thresh"]), n_sets)
 out["refine_us"] = timeit(lambda i: be.refine_matches(sets[i]["D11h"], sets[i]["D21h"], sets[i]["p1"], cfg["radius"],
                                                       cfg["dilation_max"]), n_sets)
+# whole match() call the way tracker.py:31 makes it: reference glue (torch ops) + 2 backend calls vs the fused entry
+for name, fused in (("match_unfused_us", False), ("match_fused_us", True)):
+    out[name] = timeit(lambda i, fused=fused: matching.match(sets[i]["X11"], sets[i]["X21"], sets[i]["D11h"], sets[i]["D21h"],
+                                                             fused=fused), n_sets)
+out["match_fused_f32desc_us"] = timeit(lambda i: matching.match(sets[i]["X11"], sets[i]["X21"], sets[i]["D11"], sets[i]["D21"],
+                                                                fused=True), n_sets)
+out["match_unfused_f32desc_us"] = timeit(lambda i: matching.match(sets[i]["X11"], sets[i]["X21"], sets[i]["D11"], sets[i]["D21"]),
+                                         n_sets)
 for iters in (1, 10):
     def gn(i, iters=iters):
         d = sets[i]
