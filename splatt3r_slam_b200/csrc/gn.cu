@@ -267,6 +267,8 @@ __global__ void export_blocks_kernel(const double *__restrict__ edge_blocks, int
 }  // namespace b200gn
 
 #include "gn_persistent.cuh"
+#include "gn_track.cuh"
 #include "gn_pcg.cuh"
 #include "gn_dense.cuh"
 #include "gn_api.cuh"
+#include "gn_track_api.cuh"

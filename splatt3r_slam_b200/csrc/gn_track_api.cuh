@@ -1,0 +1,66 @@
+// b200slam — C entry points of the on-device frame tracker (gn_track.cuh).  Included by gn.cu.
+#pragma once
+
+extern "C" size_t b200slam_track_workspace_bytes(void) {
+  return 256 + (size_t)1024 * b200gn::TRACK_NACC * sizeof(double);  // state + one partial per CTA (<= 1024 SMs)
+}
+
+extern "C" int b200slam_track_ray_dist(const float *Xf, const float *Xk, const float *Qk, const uint8_t *valid,
+                                       const float *T_WCf, const float *T_WCk, float *T_WCf_new, float *T_CkCf,
+                                       int n, float sigma_ray, float sigma_dist, float huber_k, int max_iters,
+                                       float rel_error, float delta_norm, void *workspace, size_t workspace_bytes,
+                                       void *stream) {
+  using namespace b200gn;
+  if (n < 0 || max_iters < 0 || !(sigma_ray > 0.0f) || !(sigma_dist > 0.0f)) return B200SLAM_EINVAL;
+  if (!T_WCf || !T_WCk || !T_WCf_new || !T_CkCf) return B200SLAM_EINVAL;
+  if (n > 0 && (!Xf || !Xk || !Qk || !valid)) return B200SLAM_EINVAL;
+  if (!workspace || workspace_bytes < b200slam_track_workspace_bytes()) return B200SLAM_EWORKSPACE;
+  static int num_sms = 0;
+  if (num_sms == 0) {
+    int dev = 0, coop = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+    if (!coop) num_sms = -1;
+  }
+  if (num_sms < 1) return B200SLAM_EINVAL;
+  const int S = num_sms > 1024 ? 1024 : num_sms;
+  int gper = (n + S - 1) / S;
+  gper = (gper + 31) / 32 * 32;
+  if (gper < 32) gper = 32;
+  if (gper > PERSIST_MAX_POINTS) return B200SLAM_EINVAL;  // > 833 k points on 148 SMs
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaError_t err = cudaFuncSetAttribute(track_ray_dist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           PERSIST_WORDS * PERSIST_MAX_POINTS * (int)sizeof(float));
+    if (err != cudaSuccess) return (int)err;
+    attr_set = true;
+  }
+  cudaStream_t st = (cudaStream_t)stream;
+  TrackState *state = (TrackState *)workspace;
+  double *partials = (double *)((char *)workspace + 256);
+  cudaError_t err = cudaMemsetAsync(state, 0, 256, st);
+  if (err != cudaSuccess) return (int)err;
+  float isr = 1.0f / sigma_ray, isd = 1.0f / sigma_dist;
+  void *args[] = {&Xf, &Xk, &Qk, &valid, &T_WCf, &T_WCk, &T_WCf_new, &T_CkCf, &n, &gper, &isr, &isd, &huber_k,
+                  &max_iters, &rel_error, &delta_norm, &partials, &state};
+  const size_t smem = (size_t)PERSIST_WORDS * gper * sizeof(float);
+  return (int)cudaLaunchCooperativeKernel((const void *)track_ray_dist_kernel, dim3(S), dim3(PERSIST_THREADS), args,
+                                          smem, st);
+}
+
+// Blocking read of the last call's outcome (synchronises `stream`).
+extern "C" int b200slam_track_status(const void *workspace, int *iters, int *converged, int *chol_fail,
+                                     double *cost, void *stream) {
+  if (!workspace) return B200SLAM_EINVAL;
+  b200gn::TrackState h;
+  cudaError_t err = cudaMemcpyAsync(&h, workspace, sizeof(h), cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+  if (err != cudaSuccess) return (int)err;
+  err = cudaStreamSynchronize((cudaStream_t)stream);
+  if (err != cudaSuccess) return (int)err;
+  if (iters) *iters = h.iters;
+  if (converged) *converged = h.converged;
+  if (chol_fail) *chol_fail = h.chol_fail;
+  if (cost) *cost = h.cost;
+  return B200SLAM_OK;
+}

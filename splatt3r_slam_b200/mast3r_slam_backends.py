@@ -49,12 +49,17 @@ def _load():
     lib.b200slam_gauss_newton.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_gauss_newton_ids.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_edge_rows.argtypes = [vp, vp, i, vp, vp, sz, vp]
+    lib.b200slam_track_workspace_bytes.argtypes = []
+    lib.b200slam_track_workspace_bytes.restype = sz
+    lib.b200slam_track_ray_dist.argtypes = [vp] * 8 + [i, f, f, f, i, f, f, vp, sz, vp]
+    lib.b200slam_track_status.argtypes = [vp, ctypes.POINTER(i), ctypes.POINTER(i), ctypes.POINTER(i),
+                                          ctypes.POINTER(ctypes.c_double), vp]
     lib.b200slam_match_workspace_bytes.argtypes = [i] * 5
     lib.b200slam_match_workspace_bytes.restype = sz
     lib.b200slam_match.argtypes = [vp] * 4 + [i] + [vp] * 3 + [i] * 5 + [f, f, f, i, i, vp, sz, vp]
     for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "gn_build_blocks",
                  "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gauss_newton",
-                 "gauss_newton_ids", "edge_rows", "match"):
+                 "gauss_newton_ids", "edge_rows", "match", "track_ray_dist", "track_status"):
         getattr(lib, "b200slam_" + name).restype = i
     return lib
 
@@ -172,6 +177,45 @@ def match(X11, X21, D11, D21, idx_1_to_2_init, max_iter, lambda_init, cost_thres
                                    float(lambda_init), float(cost_thresh), float(dist_thresh), int(radius),
                                    int(dilation_max), ws.data_ptr(), nbytes, _stream(X11)), "match")
     return [idx, valid]
+
+
+def track_ray_dist(Xf, Xk, T_WCf, T_WCk, Qk, valid, sigma_ray, sigma_dist, huber, max_iters, rel_error, delta_norm,
+                   check=True):
+    """On-device `FrameTracker.opt_pose_ray_dist_sim3` (reference tracker.py:174-214):
+    Xf (n,3) matched frame points, Xk (n,3) keyframe points, T_WCf / T_WCk Sim3 data (8,) or (1,8)
+    [t, q_xyzw, s], Qk (n,1) or (n,), valid (n,1) or (n,) bool.  Returns
+    [T_WCf_new (8,), T_CkCf (8,), info] with info = dict(iters, converged, cost) when `check`
+    (one 64-byte device->host read; the reference syncs once per iteration) else None.  A non-SPD
+    system raises RuntimeError like the reference's torch.linalg.cholesky (tracker.py:88-90)."""
+    _contig(Xf=Xf, Xk=Xk, T_WCf=T_WCf, T_WCk=T_WCk, Qk=Qk, valid=valid)
+    n = Xk.shape[0]
+    if Xf.shape != (n, 3) or Xk.shape != (n, 3) or Qk.numel() != n or valid.numel() != n:
+        raise RuntimeError("track_ray_dist: Xf, Xk must be (n,3) and Qk, valid must hold n values")
+    if T_WCf.numel() != 8 or T_WCk.numel() != 8:
+        raise RuntimeError("track_ray_dist: poses must be Sim3 data vectors of 8 floats")
+    ptrs = (_cuda(Xf, torch.float32, "Xf"), _cuda(Xk, torch.float32, "Xk"), _cuda(Qk, torch.float32, "Qk"),
+            _cuda(valid, torch.bool, "valid"), _cuda(T_WCf, torch.float32, "T_WCf"),
+            _cuda(T_WCk, torch.float32, "T_WCk"))
+    with _guard(Xk):
+        out = torch.empty((2, 8), dtype=torch.float32, device=Xk.device)
+        nbytes = _lib.b200slam_track_workspace_bytes()
+        key = ("track", Xk.device.index)
+        ws = _workspaces.get(key)
+        if ws is None:
+            ws = _workspaces[key] = torch.empty(int(nbytes), dtype=torch.uint8, device=Xk.device)
+        st = _stream(Xk)
+        _check(_lib.b200slam_track_ray_dist(*ptrs, out[0].data_ptr(), out[1].data_ptr(), n, float(sigma_ray),
+                                            float(sigma_dist), float(huber), int(max_iters), float(rel_error),
+                                            float(delta_norm), ws.data_ptr(), nbytes, st), "track_ray_dist")
+        info = None
+        if check:
+            it, cv, cf, cost = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_double()
+            _check(_lib.b200slam_track_status(ws.data_ptr(), ctypes.byref(it), ctypes.byref(cv), ctypes.byref(cf),
+                                              ctypes.byref(cost), st), "track_status")
+            if cf.value:
+                raise RuntimeError("track_ray_dist: linalg.cholesky: the normal equations are not positive-definite")
+            info = dict(iters=it.value, converged=bool(cv.value), cost=cost.value)
+    return [out[0], out[1], info]
 
 
 def edge_rows(ii, jj):

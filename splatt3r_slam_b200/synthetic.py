@@ -230,3 +230,21 @@ def make_graph_device(seed, N, E_undirected, h, w, device, edge_range=None, nois
         Q[e - e0] = 1.0 + torch.exp(0.5 * torch.randn(n, 1, generator=eg, dtype=torch.float32, device=device))
     return dict(Twc=T.float().contiguous().to(device), Twc_gt=Tgt.float(), Xs=Xs, Cs=Cs, K=sc.K.float().contiguous(),
                 ii=ii.to(device), jj=jj.to(device), idx_ii2jj=idx, valid_match=valid, Q=Q, h=h, w=w)
+
+
+def make_track_problem(seed=0, n=4096, noise=0.001, invalid=0.2, device="cpu"):
+    """Frame-to-keyframe tracking problem in the shape `FrameTracker.opt_pose_ray_dist_sim3`
+    (reference tracker.py:174) receives it: matched frame points Xf (n,3), keyframe points Xk (n,3), poses
+    T_WCf (start), T_WCk as Sim3 data (8,), match confidence Qk (n,1), valid (n,1) bool — plus the true relative
+    pose T_CkCf_gt the optimiser should recover.  A tenth of the valid points are gross outliers (Huber)."""
+    gen = torch.Generator().manual_seed(seed)
+    Xk = torch.randn(n, 3, generator=gen) * 0.5 + torch.tensor([0.0, 0.0, 2.5])
+    T_gt = random_pose(gen, rot_deg=4.0, trans=0.08, scale=0.04).float()
+    Tk = random_pose(gen, rot_deg=20.0, trans=0.5, scale=0.1).float()
+    Xf = sim3_inv_act(T_gt, Xk) + noise * torch.randn(n, 3, generator=gen)
+    out = torch.rand(n, generator=gen) < 0.1
+    Xf[out] += 0.2 * torch.randn(int(out.sum()), 3, generator=gen)
+    Qk = torch.rand(n, 1, generator=gen) * 3.0 + 0.5
+    valid = (torch.rand(n, 1, generator=gen) > invalid) & (Qk > 1.5)
+    d = dict(Xf=Xf.contiguous(), Xk=Xk.contiguous(), T_WCf=Tk.clone(), T_WCk=Tk, Qk=Qk, valid=valid, T_CkCf_gt=T_gt)
+    return {k: v.to(device) for k, v in d.items()}

@@ -1,0 +1,58 @@
+"""GPU tier: on-device frame tracker (b200slam_track_ray_dist) against the CPU
+restatement of the reference's FrameTracker.opt_pose_ray_dist_sim3 (oracle/tracker_ref.py) on the same
+seeded problems.  Floating point: poses within 1e-4 absolute, same number of Gauss-Newton steps.  The
+tolerance is set by the REFERENCE side: its normal equations have a condition number of ~1e7 (sigma_dist /
+sigma_ray = 3333, squared) and it factors them in fp32, so its own scale / depth-translation entries carry
+errors of a few 1e-5; the device path sums in fp32 but reduces and factors in fp64."""
+import pytest
+import torch
+
+from oracle import tracker_ref as tr
+from splatt3r_slam_b200 import synthetic, tracker
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-4
+
+
+def run_both(backend, P, **over):
+    cfg = dict(tracker.DEFAULT_CFG, **over)
+    D = {k: v.to("cuda:0") for k, v in P.items()}
+    Tw, Tr, info = backend.track_ray_dist(D["Xf"], D["Xk"], D["T_WCf"], D["T_WCk"], D["Qk"], D["valid"], cfg["sigma_ray"],
+                                          cfg["sigma_dist"], cfg["huber"], cfg["max_iters"], cfg["rel_error"],
+                                          cfg["delta_norm"])
+    Tw_o, Tr_o, steps = tr.opt_pose_ray_dist_sim3(P["Xf"], P["Xk"], P["T_WCf"], P["T_WCk"], P["Qk"], P["valid"],
+                                                  cfg["sigma_ray"], cfg["sigma_dist"], cfg["huber"], cfg["max_iters"],
+                                                  cfg["rel_error"], cfg["delta_norm"])
+    return Tw.cpu(), Tr.cpu(), info, Tw_o, Tr_o, steps
+
+
+@pytest.mark.parametrize("n,seed", [(64, 0), (1000, 1), (4097, 2), (196608, 3)])
+def test_track_vs_restatement(backend, n, seed):
+    P = synthetic.make_track_problem(seed=seed, n=n)
+    Tw, Tr, info, Tw_o, Tr_o, steps = run_both(backend, P)
+    assert info["iters"] == steps and info["converged"]
+    assert (Tr - Tr_o).abs().max() < TOL and (Tw - Tw_o).abs().max() < TOL
+    if n >= 1000:
+        assert (Tr - P["T_CkCf_gt"]).abs().max() < 5e-3
+
+
+def test_track_iteration_cap_and_single_step(backend):
+    P = synthetic.make_track_problem(seed=5, n=2048)
+    for cap in (1, 2):
+        Tw, Tr, info, Tw_o, Tr_o, steps = run_both(backend, P, max_iters=cap, rel_error=0.0, delta_norm=0.0)
+        assert info["iters"] == steps == cap and not info["converged"]
+        assert (Tr - Tr_o).abs().max() < TOL
+    # max_iters = 0: the start pose comes back (T_WCf = T_WCk * (T_WCk^-1 * T_WCf))
+    Tw, Tr, info, Tw_o, Tr_o, steps = run_both(backend, P, max_iters=0)
+    assert info["iters"] == 0 and (Tw - P["T_WCf"]).abs().max() < 1e-6
+
+
+def test_track_mirror_and_degenerate_system(backend):
+    P = {k: v.to("cuda:0") for k, v in synthetic.make_track_problem(seed=7, n=512).items()}
+    Tw, Tr = tracker.opt_pose_ray_dist_sim3(P["Xf"], P["Xk"], P["T_WCf"], P["T_WCk"], P["Qk"], P["valid"])
+    assert Tw.shape == (8,) and Tr.shape == (8,) and (Tr.cpu() - P["T_CkCf_gt"].cpu()).abs().max() < 5e-3
+    with pytest.raises(RuntimeError):  # no valid point -> non-SPD system -> same exception class as torch.linalg.cholesky
+        tracker.opt_pose_ray_dist_sim3(P["Xf"], P["Xk"], P["T_WCf"], P["T_WCk"], P["Qk"], torch.zeros_like(P["valid"]))
+    with pytest.raises(RuntimeError):
+        backend.track_ray_dist(P["Xf"][:, :2], P["Xk"], P["T_WCf"], P["T_WCk"], P["Qk"], P["valid"], 0.003, 10.0, 1.345,
+                               50, 1e-3, 1e-3)

@@ -117,3 +117,26 @@ def test_gn_early_exit_and_failed_factorisation(gg):
     (dx,) = oracle.gauss_newton_rays(T2, Xs, Cs, ii, jj, idx, torch.zeros_like(valid), Q, 0.003, 10.0, 0.0,
                                      1.5, 3, 1e-8)
     assert torch.equal(T2, Twc) and not dx.any() and oracle._gauss_newton.last_iters == 1
+
+
+# ---- tracker restatement (oracle/tracker_ref.py; parity unpinned, see its header) -------------------
+def test_tracker_restatement_recovers_known_pose():
+    from oracle import tracker_ref as tr
+    from splatt3r_slam_b200 import synthetic
+    P = synthetic.make_track_problem(seed=1, n=3000)
+    T_WCf, T_CkCf, steps = tr.opt_pose_ray_dist_sim3(P["Xf"], P["Xk"], P["T_WCf"], P["T_WCk"], P["Qk"], P["valid"])
+    assert 2 <= steps < 50
+    assert (T_CkCf - P["T_CkCf_gt"]).abs().max() < 5e-3      # scale and depth translation are weakly observed (sigma_dist = 10)
+    assert torch.allclose(T_WCf, tr.sim3_mul(P["T_WCk"], T_CkCf))
+    # Sim3 helpers against the pinned C oracle: Exp(0) retraction is the identity, inv * T = identity
+    ident = tr.sim3_mul(tr.sim3_inv(P["T_WCk"]), P["T_WCk"])
+    assert torch.allclose(ident, torch.tensor([0, 0, 0, 0, 0, 0, 1.0, 1.0]), atol=1e-6)
+    assert torch.allclose(tr.sim3_retr(P["T_WCk"], torch.zeros(7)), P["T_WCk"], atol=1e-7)
+
+
+def test_tracker_restatement_raises_on_degenerate_system():
+    from oracle import tracker_ref as tr
+    from splatt3r_slam_b200 import synthetic
+    P = synthetic.make_track_problem(seed=2, n=64)
+    with pytest.raises(RuntimeError):  # no valid point: H = 0, torch.linalg.cholesky raises (tracker.py:88-90)
+        tr.opt_pose_ray_dist_sim3(P["Xf"], P["Xk"], P["T_WCf"], P["T_WCk"], P["Qk"], torch.zeros_like(P["valid"]))

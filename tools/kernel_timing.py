@@ -65,6 +65,21 @@ for iters in (1, 10):
 ws = be._workspaces[("cuda", 0)]
 st = ws[:48].cpu().view(torch.int64)[2:6].tolist()
 out["gn_tracker_tail_ns"] = {"finalize": st[1] - st[0], "assemble_chol": st[2] - st[1], "finish": st[3] - st[2]}
+# on-device frame tracker (8f rank 2) on a 512x384-point problem; reference restatement on the host beside it
+import time  # noqa: E402
+from oracle import tracker_ref  # noqa: E402
+from splatt3r_slam_b200 import tracker  # noqa: E402
+TP = synthetic.make_track_problem(seed=3, n=N_PIX)
+TD = {k: v.to(dev) for k, v in TP.items()}
+c = tracker.DEFAULT_CFG
+targs = (c["sigma_ray"], c["sigma_dist"], c["huber"], c["max_iters"], c["rel_error"], c["delta_norm"])
+_, _, info = be.track_ray_dist(TD["Xf"], TD["Xk"], TD["T_WCf"], TD["T_WCk"], TD["Qk"], TD["valid"], *targs)
+out["track_ray_dist"] = {"iters": info["iters"], "us": timeit(lambda i: be.track_ray_dist(
+    TD["Xf"], TD["Xk"], TD["T_WCf"], TD["T_WCk"], TD["Qk"], TD["valid"], *targs, check=False), 1)}
+t0 = time.perf_counter()
+_, _, steps = tracker_ref.opt_pose_ray_dist_sim3(TP["Xf"], TP["Xk"], TP["T_WCf"], TP["T_WCk"], TP["Qk"], TP["valid"])
+out["track_ray_dist"]["cpu_restatement_us"] = (time.perf_counter() - t0) * 1e6
+out["track_ray_dist"]["cpu_threads"] = torch.get_num_threads()
 del sets
 torch.cuda.empty_cache()
 
