@@ -69,6 +69,25 @@ int b200slam_match(const float *X11, const float *X21, const void *D11, const vo
                    float dist_thresh, int radius, int dilation_max, void *workspace,
                    size_t workspace_bytes, void *stream);
 
+/* On-device frame-to-keyframe tracker: replaces FrameTracker.opt_pose_ray_dist_sim3 + solve +
+ * check_convergence, splatt3r_slam/tracker.py:156-214 and nonlinear_optimizer.py:5-33 (PyTorch there:
+ * ~30 kernels and one host sync per Gauss-Newton step).  NOT an entry of the reference module
+ * (SURVEY.md section 8f rank 2): tracker.py would call it instead of its own loop.
+ * Xf (n,3) frame points already gathered by the match index (tracker.py:150), Xk (n,3) keyframe points,
+ * Qk (n) match confidence, valid (n) u8; T_WCf, T_WCk: Sim3 data [t(3), q_xyzw(4), s] as lietorch stores
+ * it -> T_WCf_new = T_WCk * T_CkCf and T_CkCf (8 floats each).  One cooperative launch for the whole
+ * loop (<= max_iters steps; stops when |cost decrease| / old cost < rel_error or |tau| < delta_norm).
+ * n <= 5632 * (number of SMs).  b200slam_track_status blocks on `stream` and reports the last call's
+ * step count, convergence flag, failed-factorisation flag (the reference raises there) and final cost. */
+size_t b200slam_track_workspace_bytes(void);
+int b200slam_track_ray_dist(const float *Xf, const float *Xk, const float *Qk, const uint8_t *valid,
+                            const float *T_WCf, const float *T_WCk, float *T_WCf_new, float *T_CkCf,
+                            int n, float sigma_ray, float sigma_dist, float huber_k, int max_iters,
+                            float rel_error, float delta_norm, void *workspace, size_t workspace_bytes,
+                            void *stream);
+int b200slam_track_status(const void *workspace, int *iters, int *converged, int *chol_fail,
+                          double *cost, void *stream);
+
 /* Scalar parameters of the three GN residual models (union of the reference's scalar args,
  * gn.h:22-117).  sigma_a/sigma_b: rays = (sigma_ray, sigma_dist); calib = (sigma_pixel,
  * sigma_depth); points = (sigma_point, unused). */
