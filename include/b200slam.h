@@ -85,6 +85,16 @@ int b200slam_track_ray_dist(const float *Xf, const float *Xk, const float *Qk, c
                             int n, float sigma_ray, float sigma_dist, float huber_k, int max_iters,
                             float rel_error, float delta_norm, void *workspace, size_t workspace_bytes,
                             void *stream);
+/* Same loop for FrameTracker.opt_pose_calib_sim3, tracker.py:216-266 (residual [u, v, log z] through
+ * project_calib, geometry.py:63-105): meas_k (n,3) = [u_k, v_k, log z_k] and valid_meas_k (n) u8 as
+ * tracker.py:143-152 builds them; K device (3,3) row-major intrinsics (read by the kernel, no host sync);
+ * a projected point counts when pixel_border < u < width-1-pixel_border (same for v) and z > z_eps. */
+int b200slam_track_calib(const float *Xf, const float *meas_k, const float *Qk, const uint8_t *valid,
+                         const uint8_t *valid_meas_k, const float *K, const float *T_WCf,
+                         const float *T_WCk, float *T_WCf_new, float *T_CkCf, int n, int height,
+                         int width, float sigma_pixel, float sigma_depth, float huber_k,
+                         int pixel_border, float z_eps, int max_iters, float rel_error,
+                         float delta_norm, void *workspace, size_t workspace_bytes, void *stream);
 int b200slam_track_status(const void *workspace, int *iters, int *converged, int *chol_fail,
                           double *cost, void *stream);
 

@@ -124,3 +124,68 @@ def opt_pose_ray_dist_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, sigma_ray=0.003, sig
             break
         old_cost = new_cost
     return sim3_mul(T_WCk, T_CkCf), T_CkCf, steps
+
+
+# ---- calibrated variant (tracker.py:216-266, geometry.py:63-105) ------------------------------------
+def project_calib(P, K, img_size, border=0, z_eps=0.0):
+    b = P.shape[:-1]
+    K_rep = K.repeat(*b, 1, 1)
+    p = (K_rep @ P[..., None]).squeeze(-1)
+    p = p / p[..., 2:3]
+    p = p[..., :2]
+    u, v = p.split([1, 1], dim=-1)
+    x, y, z = P.split([1, 1, 1], dim=-1)
+    valid_u = (u > border) & (u < img_size[1] - 1 - border)
+    valid_v = (v > border) & (v < img_size[0] - 1 - border)
+    valid_z = z > z_eps
+    valid = valid_u & valid_v & valid_z
+    logz = torch.log(z)
+    logz[torch.logical_not(valid_z)] = 0.0
+    pz = torch.cat((p, logz), dim=-1)
+    fx, fy = K[0, 0], K[1, 1]
+    z_inv = 1.0 / z[..., 0]
+    dpz_dP = torch.zeros(*b + (3, 3), dtype=P.dtype)
+    dpz_dP[..., 0, 0] = fx
+    dpz_dP[..., 1, 1] = fy
+    dpz_dP[..., 0, 2] = -fx * x[..., 0] * z_inv
+    dpz_dP[..., 1, 2] = -fy * y[..., 0] * z_inv
+    dpz_dP *= z_inv[..., None, None]
+    dpz_dP[..., 2, 2] = z_inv
+    return pz, dpz_dP, valid
+
+
+def calib_measurements(Xk, img_size, depth_eps=1e-6):
+    """meas_k / valid_meas_k as FrameTracker.get_points_poses builds them (tracker.py:143-152) from
+    keyframe points that already lie on their pixel rays (constrain_points_to_ray)."""
+    h, w = img_size
+    u, v = torch.meshgrid(torch.arange(w), torch.arange(h), indexing="xy")
+    uv_k = torch.stack((u, v), dim=-1).to(Xk.dtype).view(-1, 2)
+    meas_k = torch.cat((uv_k, torch.log(Xk[..., 2:3])), dim=-1)
+    valid_meas_k = Xk[..., 2:3] > depth_eps
+    meas_k[~valid_meas_k.repeat(1, 3)] = 0.0
+    return meas_k.contiguous(), valid_meas_k
+
+
+def opt_pose_calib_sim3(Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_size, sigma_pixel=1.0,
+                        sigma_depth=10.0, huber_k=1.345, pixel_border=-10, depth_eps=1e-6, max_iters=50,
+                        rel_error=1e-3, delta_norm=1e-3):
+    sqrt_info_pixel = 1 / sigma_pixel * valid * torch.sqrt(Qk)
+    sqrt_info_depth = 1 / sigma_depth * valid * torch.sqrt(Qk)
+    sqrt_info = torch.cat((sqrt_info_pixel.repeat(1, 2), sqrt_info_depth), dim=1)
+    T_CkCf = sim3_mul(sim3_inv(T_WCk), T_WCf)
+    old_cost = float("inf")
+    steps = 0
+    for step in range(max_iters):
+        Xf_Ck, dXf_Ck_dT_CkCf = act_Sim3(T_CkCf, Xf)
+        pzf_Ck, dpzf_Ck_dXf_Ck, valid_proj = project_calib(Xf_Ck, K, img_size, border=pixel_border, z_eps=depth_eps)
+        valid2 = valid_proj & valid_meas_k
+        sqrt_info2 = valid2 * sqrt_info
+        r = meas_k - pzf_Ck
+        J = -dpzf_Ck_dXf_Ck @ dXf_Ck_dT_CkCf
+        tau, new_cost = solve(sqrt_info2, r, J, huber_k)
+        T_CkCf = sim3_retr(T_CkCf, tau)
+        steps = step + 1
+        if check_convergence(rel_error, delta_norm, old_cost, new_cost, tau):
+            break
+        old_cost = new_cost
+    return sim3_mul(T_WCk, T_CkCf), T_CkCf, steps

@@ -86,12 +86,23 @@ __device__ inline bool solve7(const double *Hu, const double *g, double *x) {
   return ok;
 }
 
+// KIND 0: ray + distance residual (opt_pose_ray_dist_sim3, tracker.py:174-214); B = Xk (n,3).
+// KIND 1: pixel + log-depth residual (opt_pose_calib_sim3, tracker.py:216-266, project_calib
+//         geometry.py:63-105); B = meas_k (n,3) = [u_k, v_k, log z_k], valid2 = valid_meas_k.
+struct TrackConsts {
+  float inv_sigma_a, inv_sigma_b, huber_k, rel_error, delta_norm;
+  float ulo, uhi, vlo, vhi, z_eps;  // calib: pixel window (border, W-1-border) x (border, H-1-border)
+  const float *K;                   // calib: device (3,3) intrinsics
+};
+
+template <int KIND>
 __global__ void __launch_bounds__(PERSIST_THREADS, 1)
-track_ray_dist_kernel(const float *__restrict__ Xf, const float *__restrict__ Xk, const float *__restrict__ Qk,
-                      const uint8_t *__restrict__ valid, const float *__restrict__ T_WCf_in,
-                      const float *__restrict__ T_WCk, float *T_WCf_out, float *T_CkCf_out, int n, int gper,
-                      float inv_sigma_ray, float inv_sigma_dist, float huber_k, int max_iters, float rel_error,
-                      float delta_norm, double *partials, TrackState *state) {
+track_kernel(const float *__restrict__ Xf, const float *__restrict__ B, const float *__restrict__ Qk,
+             const uint8_t *__restrict__ valid, const uint8_t *__restrict__ valid2,
+             const float *__restrict__ T_WCf_in, const float *__restrict__ T_WCk, float *T_WCf_out,
+             float *T_CkCf_out, int n, int gper, TrackConsts C, int max_iters, double *partials,
+             TrackState *state) {
+  const float huber_k = C.huber_k, rel_error = C.rel_error, delta_norm = C.delta_norm;
   extern __shared__ __align__(16) float pts_sm[];
   __shared__ float pose_sm[8];
   __shared__ float red[PERSIST_THREADS / 32][TRACK_NACC];
@@ -104,17 +115,24 @@ track_ray_dist_kernel(const float *__restrict__ Xf, const float *__restrict__ Xk
   // ---- prologue -------------------------------------------------------------------------------------
   for (int p = tid; p < npts; p += PERSIST_THREADS) {
     const size_t g = (size_t)p_begin + p;
-    const float xk = __ldg(Xk + 3 * g), yk = __ldg(Xk + 3 * g + 1), zk = __ldg(Xk + 3 * g + 2);
-    const float dk = sqrtf(xk * xk + yk * yk + zk * zk);  // point_to_ray_dist, geometry.py:17-24
-    const float dk_inv = 1.0f / dk;
-    const bool ok = valid[g] != 0;
+    const float xk = __ldg(B + 3 * g), yk = __ldg(B + 3 * g + 1), zk = __ldg(B + 3 * g + 2);
+    bool ok = valid[g] != 0;
     pts_sm[p] = __ldg(Xf + 3 * g);
     pts_sm[stride + p] = __ldg(Xf + 3 * g + 1);
     pts_sm[2 * stride + p] = __ldg(Xf + 3 * g + 2);
-    pts_sm[3 * stride + p] = dk_inv * xk;
-    pts_sm[4 * stride + p] = dk_inv * yk;
-    pts_sm[5 * stride + p] = dk_inv * zk;
-    pts_sm[6 * stride + p] = dk;
+    if (KIND == 0) {
+      const float dk = sqrtf(xk * xk + yk * yk + zk * zk);  // point_to_ray_dist, geometry.py:17-24
+      const float dk_inv = 1.0f / dk;
+      pts_sm[3 * stride + p] = dk_inv * xk;
+      pts_sm[4 * stride + p] = dk_inv * yk;
+      pts_sm[5 * stride + p] = dk_inv * zk;
+      pts_sm[6 * stride + p] = dk;
+    } else {
+      pts_sm[3 * stride + p] = xk;
+      pts_sm[4 * stride + p] = yk;
+      pts_sm[5 * stride + p] = zk;
+      ok = ok && valid2[g] != 0;  // tracker.py:236: valid2 = valid_proj & valid_meas_k (the constant half)
+    }
     pts_sm[7 * stride + p] = ok ? sqrtf(__ldg(Qk + g)) : 0.0f;  // tracker.py:177-178: valid * sqrt(Qk)
   }
   if (tid == 0) {  // T_CkCf = T_WCk^-1 * T_WCf (tracker.py:182): every CTA computes the same value
@@ -127,6 +145,8 @@ track_ray_dist_kernel(const float *__restrict__ Xf, const float *__restrict__ Xk
   }
   __syncthreads();
 
+  float fx = 0.0f, fy = 0.0f, cx = 0.0f, cy = 0.0f;
+  if (KIND == 1) { fx = __ldg(C.K + 0); fy = __ldg(C.K + 4); cx = __ldg(C.K + 2); cy = __ldg(C.K + 5); }
   for (int it = 0; it < max_iters; it++) {
     const float t0 = pose_sm[0], t1 = pose_sm[1], t2 = pose_sm[2], sc = pose_sm[7];
     const float q[4] = {pose_sm[3], pose_sm[4], pose_sm[5], pose_sm[6]};
@@ -140,33 +160,58 @@ track_ray_dist_kernel(const float *__restrict__ Xf, const float *__restrict__ Xk
       float R[3];
       rotate(q, X, R);
       const float P0 = fmaf(sc, R[0], t0), P1 = fmaf(sc, R[1], t1), P2 = fmaf(sc, R[2], t2);
-      const float d = sqrtf(P0 * P0 + P1 * P1 + P2 * P2), d_inv = 1.0f / d;
-      const float r0 = d_inv * P0, r1 = d_inv * P1, r2 = d_inv * P2;
-      const float e[4] = {pts_sm[3 * stride + p] - r0, pts_sm[4 * stride + p] - r1, pts_sm[5 * stride + p] - r2,
-                          pts_sm[6 * stride + p] - d};
-      const float si_ray = inv_sigma_ray * wq, si_dist = inv_sigma_dist * wq;
-      const float rr[3] = {r0, r1, r2};
+      if (KIND == 0) {
+        const float d = sqrtf(P0 * P0 + P1 * P1 + P2 * P2), d_inv = 1.0f / d;
+        const float r0 = d_inv * P0, r1 = d_inv * P1, r2 = d_inv * P2;
+        const float e[4] = {pts_sm[3 * stride + p] - r0, pts_sm[4 * stride + p] - r1, pts_sm[5 * stride + p] - r2,
+                            pts_sm[6 * stride + p] - d};
+        const float si_ray = C.inv_sigma_a * wq, si_dist = C.inv_sigma_b * wq;
+        const float rr[3] = {r0, r1, r2};
 #pragma unroll
-      for (int k = 0; k < 3; k++) {
-        float J[7];
+        for (int k = 0; k < 3; k++) {
+          float J[7];
 #pragma unroll
-        for (int c = 0; c < 3; c++) J[c] = -d_inv * ((c == k ? 1.0f : 0.0f) - rr[k] * rr[c]);
-        // [r]x row k
-        J[3] = k == 0 ? 0.0f : k == 1 ? r2 : -r1;
-        J[4] = k == 0 ? -r2 : k == 1 ? 0.0f : r0;
-        J[5] = k == 0 ? r1 : k == 1 ? -r0 : 0.0f;
-        J[6] = 0.0f;
-        const float wh = fabsf(si_ray * e[k]);
-        const float w = si_ray * si_ray * (wh < huber_k ? 1.0f : huber_k / wh);
-        accum_row<0x3fu>(acc, J, w, e[k]);
-        cost = fmaf(w * e[k], e[k], cost);
-      }
-      {
-        const float J[7] = {-r0, -r1, -r2, 0.0f, 0.0f, 0.0f, -d};
-        const float wh = fabsf(si_dist * e[3]);
-        const float w = si_dist * si_dist * (wh < huber_k ? 1.0f : huber_k / wh);
-        accum_row<0x47u>(acc, J, w, e[3]);
-        cost = fmaf(w * e[3], e[3], cost);
+          for (int c = 0; c < 3; c++) J[c] = -d_inv * ((c == k ? 1.0f : 0.0f) - rr[k] * rr[c]);
+          // [r]x row k
+          J[3] = k == 0 ? 0.0f : k == 1 ? r2 : -r1;
+          J[4] = k == 0 ? -r2 : k == 1 ? 0.0f : r0;
+          J[5] = k == 0 ? r1 : k == 1 ? -r0 : 0.0f;
+          J[6] = 0.0f;
+          const float wh = fabsf(si_ray * e[k]);
+          const float w = si_ray * si_ray * (wh < huber_k ? 1.0f : huber_k / wh);
+          accum_row<0x3fu>(acc, J, w, e[k]);
+          cost = fmaf(w * e[k], e[k], cost);
+        }
+        {
+          const float J[7] = {-r0, -r1, -r2, 0.0f, 0.0f, 0.0f, -d};
+          const float wh = fabsf(si_dist * e[3]);
+          const float w = si_dist * si_dist * (wh < huber_k ? 1.0f : huber_k / wh);
+          accum_row<0x47u>(acc, J, w, e[3]);
+          cost = fmaf(w * e[3], e[3], cost);
+        }
+      } else {
+        // project_calib (geometry.py:63-105) with K = [fx 0 cx; 0 fy cy; 0 0 1]
+        const float z_inv = 1.0f / P2;
+        const float u = fmaf(fx * P0, z_inv, cx), v = fmaf(fy * P1, z_inv, cy);
+        const bool vp = u > C.ulo && u < C.uhi && v > C.vlo && v < C.vhi && P2 > C.z_eps;
+        if (!vp) continue;  // sqrt_info2 = valid2 * sqrt_info (tracker.py:237)
+        const float e[3] = {pts_sm[3 * stride + p] - u, pts_sm[4 * stride + p] - v, pts_sm[5 * stride + p] - logf(P2)};
+        const float si_px = C.inv_sigma_a * wq, si_dep = C.inv_sigma_b * wq;
+        // rows a of dpz_dP; J = -a [I, -[P]x, P] = [-a, a x P, -a.P]
+        const float a[3][3] = {{fx * z_inv, 0.0f, -fx * P0 * z_inv * z_inv},
+                               {0.0f, fy * z_inv, -fy * P1 * z_inv * z_inv},
+                               {0.0f, 0.0f, z_inv}};
+#pragma unroll
+        for (int k = 0; k < 3; k++) {
+          const float J[7] = {-a[k][0], -a[k][1], -a[k][2],
+                              a[k][1] * P2 - a[k][2] * P1, a[k][2] * P0 - a[k][0] * P2, a[k][0] * P1 - a[k][1] * P0,
+                              -(a[k][0] * P0 + a[k][1] * P1 + a[k][2] * P2)};
+          const float si = k < 2 ? si_px : si_dep;
+          const float wh = fabsf(si * e[k]);
+          const float w = si * si * (wh < huber_k ? 1.0f : huber_k / wh);
+          accum_row<0x7fu>(acc, J, w, e[k]);
+          cost = fmaf(w * e[k], e[k], cost);
+        }
       }
     }
 #pragma unroll

@@ -52,6 +52,7 @@ def _load():
     lib.b200slam_track_workspace_bytes.argtypes = []
     lib.b200slam_track_workspace_bytes.restype = sz
     lib.b200slam_track_ray_dist.argtypes = [vp] * 8 + [i, f, f, f, i, f, f, vp, sz, vp]
+    lib.b200slam_track_calib.argtypes = [vp] * 10 + [i, i, i, f, f, f, i, f, i, f, f, vp, sz, vp]
     lib.b200slam_track_status.argtypes = [vp, ctypes.POINTER(i), ctypes.POINTER(i), ctypes.POINTER(i),
                                           ctypes.POINTER(ctypes.c_double), vp]
     lib.b200slam_match_workspace_bytes.argtypes = [i] * 5
@@ -59,7 +60,7 @@ def _load():
     lib.b200slam_match.argtypes = [vp] * 4 + [i] + [vp] * 3 + [i] * 5 + [f, f, f, i, i, vp, sz, vp]
     for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "gn_build_blocks",
                  "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gauss_newton",
-                 "gauss_newton_ids", "edge_rows", "match", "track_ray_dist", "track_status"):
+                 "gauss_newton_ids", "edge_rows", "match", "track_ray_dist", "track_calib", "track_status"):
         getattr(lib, "b200slam_" + name).restype = i
     return lib
 
@@ -198,24 +199,58 @@ def track_ray_dist(Xf, Xk, T_WCf, T_WCk, Qk, valid, sigma_ray, sigma_dist, huber
             _cuda(T_WCk, torch.float32, "T_WCk"))
     with _guard(Xk):
         out = torch.empty((2, 8), dtype=torch.float32, device=Xk.device)
-        nbytes = _lib.b200slam_track_workspace_bytes()
-        key = ("track", Xk.device.index)
-        ws = _workspaces.get(key)
-        if ws is None:
-            ws = _workspaces[key] = torch.empty(int(nbytes), dtype=torch.uint8, device=Xk.device)
+        ws, nbytes = _track_workspace(Xk.device)
         st = _stream(Xk)
         _check(_lib.b200slam_track_ray_dist(*ptrs, out[0].data_ptr(), out[1].data_ptr(), n, float(sigma_ray),
                                             float(sigma_dist), float(huber), int(max_iters), float(rel_error),
                                             float(delta_norm), ws.data_ptr(), nbytes, st), "track_ray_dist")
-        info = None
-        if check:
-            it, cv, cf, cost = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_double()
-            _check(_lib.b200slam_track_status(ws.data_ptr(), ctypes.byref(it), ctypes.byref(cv), ctypes.byref(cf),
-                                              ctypes.byref(cost), st), "track_status")
-            if cf.value:
-                raise RuntimeError("track_ray_dist: linalg.cholesky: the normal equations are not positive-definite")
-            info = dict(iters=it.value, converged=bool(cv.value), cost=cost.value)
+        info = _track_info(ws, st, "track_ray_dist") if check else None
     return [out[0], out[1], info]
+
+
+def track_calib(Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_size, sigma_pixel, sigma_depth, huber,
+                pixel_border, depth_eps, max_iters, rel_error, delta_norm, check=True):
+    """On-device `FrameTracker.opt_pose_calib_sim3` (reference tracker.py:216-266): arguments in the
+    reference's order (Xk is unused there too: the keyframe enters through meas_k (n,3) = [u, v, log z]
+    and valid_meas_k (n,1) bool, tracker.py:143-152); K (3,3) f32 on the device, img_size = (h, w).
+    Returns [T_WCf_new, T_CkCf, info] like `track_ray_dist`."""
+    _contig(Xf=Xf, T_WCf=T_WCf, T_WCk=T_WCk, Qk=Qk, valid=valid, meas_k=meas_k, valid_meas_k=valid_meas_k, K=K)
+    n = Xf.shape[0]
+    if Xf.shape != (n, 3) or meas_k.shape != (n, 3) or Qk.numel() != n or valid.numel() != n or valid_meas_k.numel() != n:
+        raise RuntimeError("track_calib: Xf, meas_k must be (n,3) and Qk, valid, valid_meas_k must hold n values")
+    if T_WCf.numel() != 8 or T_WCk.numel() != 8 or K.shape != (3, 3):
+        raise RuntimeError("track_calib: poses must be 8 floats and K (3,3)")
+    ptrs = (_cuda(Xf, torch.float32, "Xf"), _cuda(meas_k, torch.float32, "meas_k"), _cuda(Qk, torch.float32, "Qk"),
+            _cuda(valid, torch.bool, "valid"), _cuda(valid_meas_k, torch.bool, "valid_meas_k"),
+            _cuda(K, torch.float32, "K"), _cuda(T_WCf, torch.float32, "T_WCf"), _cuda(T_WCk, torch.float32, "T_WCk"))
+    with _guard(Xf):
+        out = torch.empty((2, 8), dtype=torch.float32, device=Xf.device)
+        ws, nbytes = _track_workspace(Xf.device)
+        st = _stream(Xf)
+        _check(_lib.b200slam_track_calib(*ptrs, out[0].data_ptr(), out[1].data_ptr(), n, int(img_size[0]),
+                                         int(img_size[1]), float(sigma_pixel), float(sigma_depth), float(huber),
+                                         int(pixel_border), float(depth_eps), int(max_iters), float(rel_error),
+                                         float(delta_norm), ws.data_ptr(), nbytes, st), "track_calib")
+        info = _track_info(ws, st, "track_calib") if check else None
+    return [out[0], out[1], info]
+
+
+def _track_workspace(device):
+    nbytes = _lib.b200slam_track_workspace_bytes()
+    key = ("track", device.index)
+    ws = _workspaces.get(key)
+    if ws is None:
+        ws = _workspaces[key] = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
+    return ws, nbytes
+
+
+def _track_info(ws, st, what):
+    it, cv, cf, cost = ctypes.c_int(), ctypes.c_int(), ctypes.c_int(), ctypes.c_double()
+    _check(_lib.b200slam_track_status(ws.data_ptr(), ctypes.byref(it), ctypes.byref(cv), ctypes.byref(cf),
+                                      ctypes.byref(cost), st), "track_status")
+    if cf.value:
+        raise RuntimeError(f"{what}: linalg.cholesky: the normal equations are not positive-definite")
+    return dict(iters=it.value, converged=bool(cv.value), cost=cost.value)
 
 
 def edge_rows(ii, jj):

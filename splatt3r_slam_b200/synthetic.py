@@ -248,3 +248,27 @@ def make_track_problem(seed=0, n=4096, noise=0.001, invalid=0.2, device="cpu"):
     valid = (torch.rand(n, 1, generator=gen) > invalid) & (Qk > 1.5)
     d = dict(Xf=Xf.contiguous(), Xk=Xk.contiguous(), T_WCf=Tk.clone(), T_WCk=Tk, Qk=Qk, valid=valid, T_CkCf_gt=T_gt)
     return {k: v.to(device) for k, v in d.items()}
+
+
+def make_track_problem_calib(seed=0, h=48, w=64, noise=0.001, invalid=0.2, device="cpu"):
+    """Calibrated tracking problem (`FrameTracker.opt_pose_calib_sim3`, reference tracker.py:216): the
+    keyframe points lie on the rays of the h x w pixel grid of a pinhole camera K (what
+    constrain_points_to_ray produces, tracker.py:143-144); a few have non-positive depth."""
+    gen = torch.Generator().manual_seed(seed)
+    n = h * w
+    K = torch.tensor([[0.9 * w, 0.0, 0.5 * w], [0.0, 0.9 * w, 0.5 * h], [0.0, 0.0, 1.0]])
+    v, u = torch.meshgrid(torch.arange(h, dtype=torch.float32), torch.arange(w, dtype=torch.float32), indexing="ij")
+    z = 2.0 + torch.rand(h, w, generator=gen)
+    Xk = torch.stack(((u - K[0, 2]) / K[0, 0] * z, (v - K[1, 2]) / K[1, 1] * z, z), dim=-1).view(n, 3)
+    T_gt = random_pose(gen, rot_deg=3.0, trans=0.06, scale=0.03).float()
+    Tk = random_pose(gen, rot_deg=20.0, trans=0.5, scale=0.1).float()
+    Xf = sim3_inv_act(T_gt, Xk) + noise * torch.randn(n, 3, generator=gen)
+    out = torch.rand(n, generator=gen) < 0.1
+    Xf[out] += 0.2 * torch.randn(int(out.sum()), 3, generator=gen)
+    Xk[::97, 2] = -1.0  # invalid keyframe depth (valid_meas_k false, tracker.py:150)
+    Qk = torch.rand(n, 1, generator=gen) * 3.0 + 0.5
+    valid = (torch.rand(n, 1, generator=gen) > invalid) & (Qk > 1.5)
+    d = dict(Xf=Xf.contiguous(), Xk=Xk.contiguous(), T_WCf=Tk.clone(), T_WCk=Tk, Qk=Qk, valid=valid, K=K, T_CkCf_gt=T_gt)
+    d = {k: t.to(device) for k, t in d.items()}
+    d["img_size"] = (h, w)
+    return d

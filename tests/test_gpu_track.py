@@ -56,3 +56,23 @@ def test_track_mirror_and_degenerate_system(backend):
     with pytest.raises(RuntimeError):
         backend.track_ray_dist(P["Xf"][:, :2], P["Xk"], P["T_WCf"], P["T_WCk"], P["Qk"], P["valid"], 0.003, 10.0, 1.345,
                                50, 1e-3, 1e-3)
+
+
+@pytest.mark.parametrize("h,w,seed", [(24, 32, 0), (48, 64, 1), (384, 512, 2)])
+def test_track_calib_vs_restatement(backend, h, w, seed):
+    P = synthetic.make_track_problem_calib(seed=seed, h=h, w=w)
+    meas_k, valid_meas_k = tr.calib_measurements(P["Xk"], P["img_size"])
+    c = tracker.DEFAULT_CFG
+    Tw_o, Tr_o, steps = tr.opt_pose_calib_sim3(P["Xf"], P["Xk"], P["T_WCf"], P["T_WCk"], P["Qk"], P["valid"], meas_k,
+                                               valid_meas_k, P["K"], P["img_size"])
+    g = lambda t: t.to("cuda:0")
+    Tw, Tr, info = backend.track_calib(g(P["Xf"]), g(P["Xk"]), g(P["T_WCf"]), g(P["T_WCk"]), g(P["Qk"]), g(P["valid"]),
+                                       g(meas_k), g(valid_meas_k), g(P["K"]), P["img_size"], c["sigma_pixel"],
+                                       c["sigma_depth"], c["huber"], c["pixel_border"], c["depth_eps"], c["max_iters"],
+                                       c["rel_error"], c["delta_norm"])
+    assert info["iters"] == steps and info["converged"]
+    assert (Tr.cpu() - Tr_o).abs().max() < TOL and (Tw.cpu() - Tw_o).abs().max() < TOL
+    assert (Tr.cpu() - P["T_CkCf_gt"]).abs().max() < 5e-3
+    Tw2, Tr2 = tracker.opt_pose_calib_sim3(g(P["Xf"]), g(P["Xk"]), g(P["T_WCf"]), g(P["T_WCk"]), g(P["Qk"]), g(P["valid"]),
+                                           g(meas_k), g(valid_meas_k), g(P["K"]), P["img_size"])
+    assert torch.equal(Tw2, Tw) and torch.equal(Tr2, Tr)  # deterministic: no atomics on data
