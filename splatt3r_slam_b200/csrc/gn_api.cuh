@@ -151,16 +151,21 @@ inline int launch_dense(float *Twc, const int64_t *ii_row, const int64_t *jj_row
   assemble_kernel<<<M, 256, 0, st>>>(ii_row, jj_row, edge_blocks, E, D, B.A, B.b, state);
   rc = (int)cudaGetLastError();
   if (rc) return rc;
-  static int num_sms = 0;
+  static int grid_ctas = 0;  // all co-resident: SMs x resident CTAs per SM (2 with 68 KB of shared memory each)
   const size_t smem = (size_t)DENSE_SMEM_DOUBLES * sizeof(double);
-  if (num_sms == 0) {
-    int dev = 0;
+  if (grid_ctas == 0) {
+    int dev = 0, num_sms = 0, per_sm = 0;
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
     cudaFuncSetAttribute(dense_solve_retract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dense_solve_retract_kernel, DENSE_THREADS, smem);
+    static const char *env = getenv("B200SLAM_GN_DENSE_CTAS_PER_SM");  // tuning aid
+    if (env && atoi(env) >= 1 && atoi(env) < per_sm) per_sm = atoi(env);
+    if (per_sm < 1) return B200SLAM_EINVAL;
+    grid_ctas = num_sms * per_sm;
   }
   void *args[] = {&Twc, &B, &N, &D, &delta_thresh, &dx, &state};
-  return (int)cudaLaunchCooperativeKernel((const void *)dense_solve_retract_kernel, dim3(num_sms), dim3(DENSE_THREADS),
+  return (int)cudaLaunchCooperativeKernel((const void *)dense_solve_retract_kernel, dim3(grid_ctas), dim3(DENSE_THREADS),
                                           args, smem, st);
 }
 
