@@ -30,6 +30,25 @@ if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
 
 import torch
 
+# ... and torch's NCCL process group prints the banner anyway on some builds: keep the real stdout for the
+# one JSON line and send everything else written to fd 1 (by any library, any thread) to stderr.
+if __name__ == "__main__" and "_B200SLAM_STDOUT_FD" not in os.environ:
+    sys.stdout.flush()
+    os.environ["_B200SLAM_STDOUT_FD"] = str(os.dup(1))
+    os.dup2(2, 1)
+
+
+def emit(line):
+    """The bench contract's ONE JSON line, on the process's original stdout."""
+    data = (json.dumps(line) + "\n").encode()
+    fd = os.environ.get("_B200SLAM_STDOUT_FD")
+    if fd is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(int(fd), data)
+
+
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
@@ -130,7 +149,7 @@ def run_reference(args):
             "config": {"workload": "tracker step 512x384 24-d: iter_proj+refine_matches (b=1) + gauss_newton_rays N=2 E=2 10 iters"},
             "cpu_baseline": {"value": val, "unit": "px/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": val, "unit": "px/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def main():

@@ -6,7 +6,7 @@ import time
 import torch
 import torch.distributed as dist
 
-from bench import (B_GN_EDGE, B_GN_POINT, B_ITER_PROJ, B_REFINE, FDIM, GN, H, N_PIX, W, ClockSampler, make_sets,
+from bench import (emit, B_GN_EDGE, B_GN_POINT, B_ITER_PROJ, B_REFINE, FDIM, GN, H, N_PIX, W, ClockSampler, make_sets,
                    peaks)
 
 
@@ -190,7 +190,7 @@ def run_tracker(args):
     }
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline_tracker()
-    print(json.dumps(line))
+    emit(line)
 
 
 def _kernel_times(be, cfg, sets, steps):
@@ -232,4 +232,4 @@ def run_graph(args):
     rank, world, local = _init_dist(args)
     line = bench_graph(args, rank, world, local)
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
