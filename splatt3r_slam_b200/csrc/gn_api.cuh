@@ -146,6 +146,9 @@ inline int launch_dense(float *Twc, const int64_t *ii_row, const int64_t *jj_row
   B.bar = reinterpret_cast<unsigned *>(ws + L.dense_ctrl);
   B.flag = reinterpret_cast<int *>(ws + L.dense_ctrl + 64);
   B.W = reinterpret_cast<double *>(ws + L.dense_ctrl + 256);
+  // x: the PCG solver's solution vector (same workspace region; the two solvers never run together)
+  B.x = reinterpret_cast<double *>(ws + L.pcg + 256 + align256((2 * (size_t)M + 2 + 2 * (size_t)E) * sizeof(int))) +
+        (size_t)49 * M + D;
   int rc = (int)cudaMemsetAsync(ws + L.dense_ctrl, 0, 256, st);
   if (rc) return rc;
   assemble_kernel<<<M, 256, 0, st>>>(ii_row, jj_row, edge_blocks, E, D, B.A, B.b, state);

@@ -21,7 +21,8 @@ constexpr int DENSE_SMEM_DOUBLES = 2 * DT * DLD + 2 * DT;  // As, Bs, two 64-vec
 
 struct DenseBufs {
   double *A;       // (D,D) row-major, lower triangle valid on entry, overwritten by L (off-diagonal tiles)
-  double *b;       // (D) rhs in, solution out
+  double *b;       // (D) rhs in, y = L^-1 b out
+  double *x;       // (D) solution of L^T x = y
   double *W;       // (nt, 64, 64) inverses of the diagonal tiles, row-major, zero above the diagonal
   unsigned *bar;   // grid barrier [counter, generation]
   int *flag;       // non-positive pivot
@@ -336,35 +337,59 @@ dense_solve_retract_kernel(float *Twc, DenseBufs B, int N, int D, float delta_th
       state->t[3] = (unsigned long long)(clock64() - c_start);
     }
   }
-  // ---- backward substitution L^T x = y, one tile row at a time from the bottom --------------------------
+  // ---- backward substitution L^T x = y, one tile row per step from the bottom, ONE barrier per step:
+  // every CTA with a tile in the row derives x_kk = W_kk^T y_kk itself (32 KB of W from L2; x goes to its own
+  // array so nobody reads a half-written y_kk), then updates its y_i -= L_{kk,i}^T x_kk.  Loads are issued
+  // 16 at a time per thread (the one-at-a-time version spent 45 k cycles per tile on L2 round trips).
   if (ok) {
+    double *xs = v0, *red = As;  // xs[64]; red[4][64] partial sums
+    const int c = tid & 63, part = tid >> 6;
     for (int kk = nt - 1; kk >= 0; kk--) {
       const int k0 = kk * DT, ts = min(DT, D - k0);
-      if (cta == 0) {  // x_kk = W_kk^T y_kk
-        if (tid < DT) v0[tid] = tid < ts ? __ldcg(B.b + k0 + tid) : 0.0;
-        __syncthreads();
-        if (tid < ts) {
+      if (cta < kk || cta == 0) {
+        {
           const double *Wg = B.W + (size_t)kk * DT * DT;
-          double s = 0.0;
-          for (int i = tid; i < ts; i++) s += __ldcg(Wg + i * DT + tid) * v0[i];
-          B.b[k0 + tid] = s;
+          double w[16], y[16];
+#pragma unroll
+          for (int u = 0; u < 16; u++) {
+            const int i = part * 16 + u;
+            w[u] = __ldcg(Wg + i * DT + c);
+            y[u] = i < ts ? __ldcg(B.b + k0 + i) : 0.0;
+          }
+          double sacc = 0.0;
+#pragma unroll
+          for (int u = 0; u < 16; u++) sacc += w[u] * y[u];
+          red[part * DT + c] = sacc;
         }
-      }
-      grid_barrier(B.bar, gen);
-      for (int i = cta; i < kk; i += G) {  // y_i -= L_{kk,i}^T x_kk
-        if (tid < DT) v0[tid] = tid < ts ? __ldcg(B.b + k0 + tid) : 0.0;
         __syncthreads();
         if (tid < DT) {
-          double s = 0.0;
-          for (int r = 0; r < ts; r++) s += __ldcg(B.A + (size_t)(k0 + r) * ld + i * DT + tid) * v0[r];
-          B.b[i * DT + tid] = __ldcg(B.b + i * DT + tid) - s;
+          const double xv = (red[tid] + red[DT + tid]) + (red[2 * DT + tid] + red[3 * DT + tid]);
+          xs[tid] = tid < ts ? xv : 0.0;
+          if (cta == 0 && tid < ts) B.x[k0 + tid] = xv;
         }
         __syncthreads();
+        for (int i = cta; i < kk; i += G) {  // y_i -= L_{kk,i}^T x_kk
+          double lv[16];
+#pragma unroll
+          for (int u = 0; u < 16; u++) {
+            const int r = part * 16 + u;
+            lv[u] = r < ts ? __ldcg(B.A + (size_t)(k0 + r) * ld + i * DT + c) : 0.0;
+          }
+          double sacc = 0.0;
+#pragma unroll
+          for (int u = 0; u < 16; u++) sacc += lv[u] * xs[part * 16 + u];
+          red[part * DT + c] = sacc;
+          __syncthreads();
+          if (tid < DT)
+            B.b[i * DT + tid] = __ldcg(B.b + i * DT + tid) -
+                                ((red[tid] + red[DT + tid]) + (red[2 * DT + tid] + red[3 * DT + tid]));
+          __syncthreads();
+        }
       }
       grid_barrier(B.bar, gen);
     }
   }
-  if (cta == 0) finish_update(ok, B.b, fin_scratch, D, N, Twc, dx, delta_thresh, state);
+  if (cta == 0) finish_update(ok, B.x, fin_scratch, D, N, Twc, dx, delta_thresh, state);
 }
 
 }  // namespace b200gn

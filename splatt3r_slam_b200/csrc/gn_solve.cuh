@@ -101,30 +101,45 @@ assemble_kernel(const int64_t *__restrict__ ii_row, const int64_t *__restrict__ 
   double *strip = A + (size_t)7 * r * D;
   for (int t = threadIdx.x; t < 7 * D; t += blockDim.x) strip[t] = 0.0;
   __syncthreads();
-  const int t = threadIdx.x;
-  if (t < 56) {
-    const int k = t / 7, l = t % 7;  // t in [49,56): rhs component l
-    double accb = 0.0;
-    for (int e = 0; e < E; e++) {
-      const int i = (int)ii_row[e] - NUM_FIX, j = (int)jj_row[e] - NUM_FIX;
-      if (i != r && j != r) continue;
-      const double v = edge_blocks[(size_t)e * 56 + t];
-      if (t < 49) {
-        if (i == r) {
-          strip[(size_t)k * D + 7 * i + l] += v;
-          if (j >= 0) strip[(size_t)k * D + 7 * j + l] -= v;
+  // The CTA scans the edge list 256 edges at a time (ballot per warp); threads 0..55 then visit only the
+  // incident edges of the chunk, in edge order (a serial scan of E = 8192 edges per pose cost 2.8 ms).
+  __shared__ unsigned incident[8];
+  const int t = threadIdx.x, k = t / 7, l = t % 7;  // t in [49,56): rhs component l
+  double accb = 0.0;
+  for (int base = 0; base < E; base += 256) {
+    const int e = base + t;
+    bool hit = false;
+    if (e < E) hit = ((int)ii_row[e] - NUM_FIX == r) || ((int)jj_row[e] - NUM_FIX == r);
+    const unsigned m = __ballot_sync(0xffffffffu, hit);
+    if ((t & 31) == 0) incident[t >> 5] = m;
+    __syncthreads();
+    if (t < 56) {
+      for (int w = 0; w < 8; w++) {
+        unsigned mm = incident[w];
+        while (mm) {
+          const int e2 = base + 32 * w + __ffs(mm) - 1;
+          mm &= mm - 1;
+          const int i = (int)ii_row[e2] - NUM_FIX, j = (int)jj_row[e2] - NUM_FIX;
+          const double v = edge_blocks[(size_t)e2 * 56 + t];
+          if (t < 49) {
+            if (i == r) {
+              strip[(size_t)k * D + 7 * i + l] += v;
+              if (j >= 0) strip[(size_t)k * D + 7 * j + l] -= v;
+            }
+            if (j == r) {
+              strip[(size_t)k * D + 7 * j + l] += v;
+              if (i >= 0) strip[(size_t)k * D + 7 * i + l] -= v;
+            }
+          } else {
+            if (i == r) accb -= v;  // g_i = -g_j
+            if (j == r) accb += v;
+          }
         }
-        if (j == r) {
-          strip[(size_t)k * D + 7 * j + l] += v;
-          if (i >= 0) strip[(size_t)k * D + 7 * i + l] -= v;
-        }
-      } else {
-        if (i == r) accb -= v;  // g_i = -g_j
-        if (j == r) accb += v;
       }
     }
-    if (t >= 49) rhs[7 * r + l] = accb;
+    __syncthreads();
   }
+  if (t >= 49 && t < 56) rhs[7 * r + l] = accb;
 }
 
 // ---- Sim3 exponential / retraction (expSO3 :298-320, expSim3 :322-389, retrSim3 :391-412) -----
