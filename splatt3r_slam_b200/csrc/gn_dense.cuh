@@ -17,7 +17,9 @@ namespace b200gn {
 constexpr int DT = 64;               // tile edge
 constexpr int DLD = DT + 2;          // leading dimension of the transposed staging tiles (16-byte aligned rows)
 constexpr int DENSE_THREADS = 256;   // 16 x 16 threads, 4 x 4 outputs each
-constexpr int DENSE_SMEM_DOUBLES = 2 * DT * DLD + 2 * DT;  // As, Bs, two 64-vectors
+constexpr int GLD = DT + 4;          // leading dimension of the row-major GEMM operand tiles: 8 rows x 4 k-columns of an
+                                     // mma fragment land on 32 distinct banks (row stride 136 words = 8 mod 32)
+constexpr int DENSE_SMEM_DOUBLES = 2 * DT * GLD + 2 * DT;  // As, Bs, two 64-vectors
 
 struct DenseBufs {
   double *A;       // (D,D) row-major, lower triangle valid on entry, overwritten by L (off-diagonal tiles)
@@ -28,11 +30,10 @@ struct DenseBufs {
   int *flag;       // non-positive pivot
 };
 
-// S[k * DLD + r] = G[r * ld + k]  (transposed staging; zero outside rows x cols).  All 16 loads of a
-// thread are issued before the first store: one L2 round trip per tile instead of sixteen (the
-// one-at-a-time version made a tile cost ~44 k cycles against 4 k for its 64^3 DFMAs).
-__device__ __forceinline__ void stage_tile_T(double *__restrict__ S, const double *__restrict__ G, size_t ld, int rows,
-                                             int cols) {
+// S[r * GLD + k] = G[r * ld + k]  (zero outside rows x cols).  All 16 loads of a thread are issued before
+// the first store: one L2 round trip per tile instead of sixteen.
+__device__ __forceinline__ void stage_tile(double *__restrict__ S, const double *__restrict__ G, size_t ld, int rows,
+                                           int cols) {
   double v[DT * DT / DENSE_THREADS];
 #pragma unroll
   for (int u = 0; u < DT * DT / DENSE_THREADS; u++) {
@@ -42,34 +43,39 @@ __device__ __forceinline__ void stage_tile_T(double *__restrict__ S, const doubl
 #pragma unroll
   for (int u = 0; u < DT * DT / DENSE_THREADS; u++) {
     const int t = threadIdx.x + u * DENSE_THREADS, r = t >> 6, k = t & 63;
-    S[k * DLD + r] = v[u];
+    S[r * GLD + k] = v[u];
   }
 }
 
-// Column owned by accumulator slot c of thread column tx: {2tx, 2tx+1, 32+2tx, 33+2tx}.  With 4tx + c a
-// half-warp's 16-byte B reads sat at a 32-byte stride (2-way bank conflict: 4 wavefronts per load);
-// this way they are contiguous (2 wavefronts), and the C-tile rows are read/written as 16-byte pairs.
-__device__ __forceinline__ int dcol(int tx, int c) { return (c < 2 ? 0 : 30) + 2 * tx + c; }
-
-// acc[a][c] = sum_k As[k][4*ty + a] * Bs[k][dcol(tx, c)]   (C = A B^T on the staged tiles)
+// fp64 tensor-core tile product C = A B^T on staged row-major operands As[r][k], Bs[c][k] (64 x 64 x kmax):
+// mma.sync.m8n8k4 (DMMA).  Warp w owns rows 16*(w>>1)..+16 and columns 32*(w&1)..+32 = 2 x 4 mma tiles; per
+// 4-wide k step it loads 2 + 4 fragments (one double per lane each, conflict-free) for 8 DMMAs = 2048 FMAs.
+// The scalar version (4 x 4 register tiles) needed four 128-bit shared loads per 16 DFMAs and was bound by
+// shared-memory wavefronts at a third of the fp64 peak.
+// acc[mi][ni][0..1] = C[16*(w>>1) + 8*mi + (lane>>2)][32*(w&1) + 8*ni + 2*(lane&3) + {0,1}]
 __device__ __forceinline__ void tile_gemm(const double *__restrict__ As, const double *__restrict__ Bs, int kmax,
-                                          double (&acc)[4][4]) {
-  const int ty = threadIdx.x >> 4, tx = threadIdx.x & 15;
+                                          double (&acc)[2][4][2]) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, g = lane >> 2, q = lane & 3;
+  const double *ap = As + (16 * (w >> 1) + g) * GLD + q;
+  const double *bp = Bs + (32 * (w & 1) + g) * GLD + q;
 #pragma unroll
-  for (int a = 0; a < 4; a++)
+  for (int mi = 0; mi < 2; mi++)
 #pragma unroll
-    for (int c = 0; c < 4; c++) acc[a][c] = 0.0;
+    for (int ni = 0; ni < 4; ni++) acc[mi][ni][0] = acc[mi][ni][1] = 0.0;
 #pragma unroll 4
-  for (int k = 0; k < kmax; k++) {
-    const double2 a01 = *reinterpret_cast<const double2 *>(As + k * DLD + 4 * ty);
-    const double2 a23 = *reinterpret_cast<const double2 *>(As + k * DLD + 4 * ty + 2);
-    const double2 b01 = *reinterpret_cast<const double2 *>(Bs + k * DLD + 2 * tx);
-    const double2 b23 = *reinterpret_cast<const double2 *>(Bs + k * DLD + 32 + 2 * tx);
-    const double av[4] = {a01.x, a01.y, a23.x, a23.y}, bv[4] = {b01.x, b01.y, b23.x, b23.y};
+  for (int k4 = 0; k4 < kmax; k4 += 4) {  // operands are zero-padded beyond kmax
+    double a[2], b[4];
 #pragma unroll
-    for (int a = 0; a < 4; a++)
+    for (int mi = 0; mi < 2; mi++) a[mi] = ap[mi * 8 * GLD + k4];
 #pragma unroll
-      for (int c = 0; c < 4; c++) acc[a][c] += av[a] * bv[c];
+    for (int ni = 0; ni < 4; ni++) b[ni] = bp[ni * 8 * GLD + k4];
+#pragma unroll
+    for (int mi = 0; mi < 2; mi++)
+#pragma unroll
+      for (int ni = 0; ni < 4; ni++)
+        asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};"
+                     : "+d"(acc[mi][ni][0]), "+d"(acc[mi][ni][1])
+                     : "d"(a[mi]), "d"(b[ni]));
   }
 }
 
@@ -202,32 +208,36 @@ __device__ __noinline__ void dense_factor_diag(const DenseBufs &B, int kk, int D
   __syncthreads();
 }
 
-// Trailing tile A_ij -= L_ik L_jk^T (column kk = k0 / DT).  staged_i: row tile currently held in As.
-__device__ __forceinline__ void dense_trail_tile(const DenseBufs &B, int D, int k0, int ts, int i, int j, int &staged_i,
-                                                 double *As, double *Bs) {
-  const int tid = threadIdx.x, ty = tid >> 4, tx = tid & 15;
+// Trailing tile A_ij -= L_ik L_jk^T on staged operands (As = L_ik rows, Bs = L_jk rows).  `wait` is called after
+// the old values of the target tile have been requested (their L2 latency hides under the product) and must
+// make the staged operands visible to the CTA.
+template <class Wait>
+__device__ __forceinline__ void dense_trail_compute(const DenseBufs &B, int D, int ts, int i, int j, const double *As,
+                                                    const double *Bs, Wait wait) {
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5, g = lane >> 2, q = lane & 3;
   const size_t ld = (size_t)D;
   const int rows_i = min(DT, D - i * DT), rows_j = min(DT, D - j * DT);
-  if (i != staged_i) {
-    stage_tile_T(As, B.A + (size_t)(i * DT) * ld + k0, ld, rows_i, ts);
-    staged_i = i;
-  }
-  stage_tile_T(Bs, B.A + (size_t)(j * DT) * ld + k0, ld, rows_j, ts);
-  __syncthreads();
-  // the old values of the target tile are fetched BEFORE the product so their L2 latency hides under it
-  double *ct = B.A + (size_t)(i * DT + 4 * ty) * ld + j * DT;
-  double cold[4][4], acc[4][4];
+  const int r0 = 16 * (w >> 1) + g, c0 = 32 * (w & 1) + 2 * q;
+  double *ct = B.A + (size_t)(i * DT + r0) * ld + j * DT + c0;
+  double cold[2][4][2], acc[2][4][2];
 #pragma unroll
-  for (int a = 0; a < 4; a++)
+  for (int mi = 0; mi < 2; mi++)
 #pragma unroll
-    for (int c = 0; c < 4; c++)
-      cold[a][c] = (4 * ty + a < rows_i && dcol(tx, c) < rows_j) ? __ldcg(ct + (size_t)a * ld + dcol(tx, c)) : 0.0;
+    for (int ni = 0; ni < 4; ni++)
+#pragma unroll
+      for (int e = 0; e < 2; e++)
+        cold[mi][ni][e] = (r0 + 8 * mi < rows_i && c0 + 8 * ni + e < rows_j)
+                              ? __ldcg(ct + (size_t)(8 * mi) * ld + 8 * ni + e) : 0.0;
+  wait();
   tile_gemm(As, Bs, ts, acc);
 #pragma unroll
-  for (int a = 0; a < 4; a++)
+  for (int mi = 0; mi < 2; mi++)
 #pragma unroll
-    for (int c = 0; c < 4; c++)
-      if (4 * ty + a < rows_i && dcol(tx, c) < rows_j) ct[(size_t)a * ld + dcol(tx, c)] = cold[a][c] - acc[a][c];
+    for (int ni = 0; ni < 4; ni++)
+#pragma unroll
+      for (int e = 0; e < 2; e++)
+        if (r0 + 8 * mi < rows_i && c0 + 8 * ni + e < rows_j)
+          ct[(size_t)(8 * mi) * ld + 8 * ni + e] = cold[mi][ni][e] - acc[mi][ni][e];
   __syncthreads();
 }
 
@@ -235,17 +245,16 @@ __global__ void __launch_bounds__(DENSE_THREADS, 2)
 dense_solve_retract_kernel(float *Twc, DenseBufs B, int N, int D, float delta_thresh, float *dx, State *state) {
   if (state->done) return;  // written only at the end of an earlier launch: uniform over the grid
   extern __shared__ __align__(16) double dsm[];
-  double *As = dsm, *Bs = dsm + DT * DLD, *v0 = dsm + 2 * DT * DLD;
+  double *As = dsm, *Bs = dsm + DT * GLD, *v0 = dsm + 2 * DT * GLD;
   __shared__ int fail;
   __shared__ double fin_scratch[64];
   const int tid = threadIdx.x, G = gridDim.x, cta = blockIdx.x;
-  const int ty = tid >> 4, tx = tid & 15;
   const int nt = (D + DT - 1) / DT;
   const size_t ld = (size_t)D;
   unsigned gen = 0;
   if (tid == 0) gen = ld_acquire_u32(&B.bar[1]);
   bool ok = true;
-  double acc[4][4];
+  double acc[2][4][2];
   // cycle counts for tools/dense_probe.py: [0] diagonal factorisations (CTA 0), [1] panel work, [2] trailing
   // work, [3] whole kernel (CTA 1, or CTA 0 on a one-CTA grid)
   long long c_diag = 0, c_panel = 0, c_trail = 0, c_t;
@@ -258,12 +267,38 @@ dense_solve_retract_kernel(float *Twc, DenseBufs B, int N, int D, float delta_th
   //   (3b) CTA 0 factors the diagonal tile kk+1 (serial: ~100 k cycles) WHILE the other CTAs do the
   //        rest of the trailing update — the look-ahead hides the serial step whenever a CTA's share
   //        of the trailing tiles takes longer than one diagonal factorisation.
+  // Workers of phase (3b): every CTA that does NOT share an SM with CTA 0 — a co-resident CTA running DMMAs
+  // slowed the serial diagonal factorisation from ~61 k to ~114 k cycles per tile.  SM ids are exchanged
+  // through the head of the (not yet used) solution vector.
+  __shared__ int s_wc, s_WG;
+  {
+    unsigned smid;
+    asm volatile("mov.u32 %0, %%smid;" : "=r"(smid));
+    int *smids = reinterpret_cast<int *>(B.x);
+    if (tid == 0) smids[cta] = (int)smid;
+  }
   if (cta == 0) {
     c_t = clock64();
     dense_factor_diag(B, 0, D, As, Bs, v0, &fail);
     c_diag += clock64() - c_t;
   }
   grid_barrier(B.bar, gen);
+  if (tid == 0) {
+    const int *smids = reinterpret_cast<const int *>(B.x);
+    const int sm0 = __ldcg(smids), mine = __ldcg(smids + cta);
+    int wc = 0, WG = 0;
+    for (int c = 1; c < G; c++) {
+      const bool worker = __ldcg(smids + c) != sm0;
+      if (worker && c < cta) wc++;
+      if (worker) WG++;
+    }
+    s_WG = WG;
+    s_wc = (cta > 0 && mine != sm0) ? wc : -1;  // -1: idles in (3b)
+    if (G == 1 || WG == 0) { s_WG = 1; s_wc = cta == 0 ? 0 : -1; }  // CTA 0 does everything itself
+  }
+  __syncthreads();
+  const int wc3b = s_wc, WG3b = s_WG;
+  const bool diag_also_works = (G == 1) || (WG3b == 1 && wc3b == 0 && cta == 0);
   if (__ldcg(B.flag)) ok = false;
   for (int kk = 0; ok && kk < nt; kk++) {
     const int k0 = kk * DT, ts = min(DT, D - k0);
@@ -271,24 +306,29 @@ dense_solve_retract_kernel(float *Twc, DenseBufs B, int N, int D, float delta_th
     c_t = clock64();
     for (int i = kk + 1 + cta; i < nt; i += G) {
       const int rows = min(DT, D - i * DT);
-      stage_tile_T(As, B.A + (size_t)(i * DT) * ld + k0, ld, rows, ts);
-      stage_tile_T(Bs, B.W + (size_t)kk * DT * DT, DT, DT, DT);
+      stage_tile(As, B.A + (size_t)(i * DT) * ld + k0, ld, rows, ts);
+      stage_tile(Bs, B.W + (size_t)kk * DT * DT, DT, DT, DT);
       if (tid < DT) v0[tid] = tid < ts ? __ldcg(B.b + k0 + tid) : 0.0;
       __syncthreads();
       tile_gemm(As, Bs, ts, acc);
       __syncthreads();
+      {
+        const int lane = tid & 31, w = tid >> 5, r0 = 16 * (w >> 1) + (lane >> 2), c0 = 32 * (w & 1) + 2 * (lane & 3);
 #pragma unroll
-      for (int a = 0; a < 4; a++)
+        for (int mi = 0; mi < 2; mi++)
 #pragma unroll
-        for (int c = 0; c < 4; c++) {
-          const int r = 4 * ty + a, cc = dcol(tx, c);
-          As[r * DLD + cc] = acc[a][c];
-          if (r < rows && cc < ts) B.A[(size_t)(i * DT + r) * ld + k0 + cc] = acc[a][c];
-        }
+          for (int ni = 0; ni < 4; ni++)
+#pragma unroll
+            for (int e = 0; e < 2; e++) {
+              const int r = r0 + 8 * mi, cc = c0 + 8 * ni + e;
+              As[r * GLD + cc] = acc[mi][ni][e];
+              if (r < rows && cc < ts) B.A[(size_t)(i * DT + r) * ld + k0 + cc] = acc[mi][ni][e];
+            }
+      }
       __syncthreads();
       if (tid < rows) {
         double s = 0.0;
-        for (int c = 0; c < ts; c++) s += As[tid * DLD + c] * v0[c];
+        for (int c = 0; c < ts; c++) s += As[tid * GLD + c] * v0[c];
         B.b[i * DT + tid] = __ldcg(B.b + i * DT + tid) - s;
       }
       __syncthreads();
@@ -299,9 +339,10 @@ dense_solve_retract_kernel(float *Twc, DenseBufs B, int N, int D, float delta_th
     if (m == 0) break;
     c_t = clock64();
     // ---- (3a) trailing tiles of column kk+1: A_{i,kk+1} -= L_ik L_{kk+1,k}^T ------------------------------
-    {
-      int staged_i = -1;
-      for (int i = kk + 1 + cta; i < nt; i += G) dense_trail_tile(B, D, k0, ts, i, kk + 1, staged_i, As, Bs);
+    for (int i = kk + 1 + cta; i < nt; i += G) {
+      stage_tile(As, B.A + (size_t)(i * DT) * ld + k0, ld, min(DT, D - i * DT), ts);
+      stage_tile(Bs, B.A + (size_t)((kk + 1) * DT) * ld + k0, ld, min(DT, D - (kk + 1) * DT), ts);
+      dense_trail_compute(B, D, ts, i, kk + 1, As, Bs, [] { __syncthreads(); });
     }
     c_trail += clock64() - c_t;
     grid_barrier(B.bar, gen);
@@ -312,17 +353,30 @@ dense_solve_retract_kernel(float *Twc, DenseBufs B, int N, int D, float delta_th
       c_diag += clock64() - c_t;
       c_t = clock64();
     }
-    if (cta > 0 || G == 1) {
-      const int WG = G == 1 ? 1 : G - 1, wc = G == 1 ? 0 : cta - 1, m2 = m - 1;
+    if (wc3b >= 0 && (cta > 0 || diag_also_works)) {
+      const int WG = WG3b, wc = wc3b, m2 = m - 1;
       const long long total = (long long)m2 * (m2 + 1) / 2;
       const long long per = (total + WG - 1) / WG, t_begin = per * wc, t_end = min(total, t_begin + per);
-      int staged_i = -1;  // consecutive items share the row tile i: L_ik stays staged in As
-      for (long long t = t_begin; t < t_end; t++) {
-        int ip = (int)((sqrt(8.0 * (double)t + 1.0) - 1.0) * 0.5);
-        while ((long long)(ip + 1) * (ip + 2) / 2 <= t) ip++;
-        while ((long long)ip * (ip + 1) / 2 > t) ip--;
-        const int jp = (int)(t - (long long)ip * (ip + 1) / 2);
-        dense_trail_tile(B, D, k0, ts, kk + 2 + ip, kk + 2 + jp, staged_i, As, Bs);
+      // consecutive items share the row tile i: L_ik stays staged in As.  (Streaming the next L_jk with 8-byte
+      // cp.async into a second buffer was measured 25 % SLOWER: 4096 tiny async copies per tile; rows of an
+      // odd-D matrix are not 16-byte aligned.)
+      if (t_begin < t_end) {
+        int ip = (int)((sqrt(8.0 * (double)t_begin + 1.0) - 1.0) * 0.5);
+        while ((long long)(ip + 1) * (ip + 2) / 2 <= t_begin) ip++;
+        while ((long long)ip * (ip + 1) / 2 > t_begin) ip--;
+        int jp = (int)(t_begin - (long long)ip * (ip + 1) / 2);
+        int staged_i = -1;
+        for (long long t = t_begin; t < t_end; t++) {
+          const int i = kk + 2 + ip, j = kk + 2 + jp;
+          if (i != staged_i) {
+            stage_tile(As, B.A + (size_t)(i * DT) * ld + k0, ld, min(DT, D - i * DT), ts);
+            staged_i = i;
+          }
+          stage_tile(Bs, B.A + (size_t)(j * DT) * ld + k0, ld, min(DT, D - j * DT), ts);
+          dense_trail_compute(B, D, ts, i, j, As, Bs, [] { __syncthreads(); });
+          if (jp < ip) jp++;
+          else { ip++; jp = 0; }
+        }
       }
       c_trail += clock64() - c_t;
     }
