@@ -18,5 +18,11 @@ for _ in range(3):
     T = s["Twc"].clone()
     be.gauss_newton_rays(T, s["Xs"], s["Cs"], s["ii"], s["jj"], s["idx_ii2jj"], s["valid_match"], s["Q"],
                          GN["sigma_ray"], GN["sigma_dist"], GN["C_thresh"], GN["Q_thresh"], 3, 0.0)
+    # the two entries beyond the reference module
+    matching.match(s["X11"], s["X21"], D11h, D21h, fused=True)
+from splatt3r_slam_b200 import synthetic, tracker
+TP = {k: v.to(dev) for k, v in synthetic.make_track_problem(seed=3, n=N_PIX).items()}
+for _ in range(2):
+    tracker.opt_pose_ray_dist_sim3(TP["Xf"], TP["Xk"], TP["T_WCf"], TP["T_WCk"], TP["Qk"], TP["valid"])
 torch.cuda.synchronize()
 print("ok")
