@@ -125,6 +125,14 @@ def bench_graph(args, rank, world, local):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    sampler = None
+    if rank == 0:
+        try:  # SM clocks / throttle reasons under load (bench.py's sampler; absent when used outside the bench)
+            from bench import ClockSampler
+            sampler = ClockSampler(local)
+            sampler.start()
+        except Exception:
+            sampler = None
     a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     a.record()
     for _ in range(args.steps):
@@ -133,6 +141,9 @@ def bench_graph(args, rank, world, local):
     if world > 1:
         dist.barrier()
     torch.cuda.synchronize()
+    if sampler is not None:
+        sampler.stop_flag = True
+        sampler.join(timeout=10)
     t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -165,4 +176,5 @@ def bench_graph(args, rank, world, local):
         "roofline": {"bound": "hbm", "kernel": "gn build (whole iteration incl. solve + allreduce)", "achieved": ach,
                      "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": src},
         "ranks_bit_identical": same, "gpu_launches": args.steps * iters * 4,
+        "clocks": sampler.result() if sampler is not None else None,
     }
