@@ -181,7 +181,7 @@ def run_tracker(args):
         "match_px_per_s": N_PIX / ((kt["iter_proj"] + kt["refine"]) * 1e-6),
         "gn_iters_per_s": {"E2": GN["iters"] / (kt["gn"] * 1e-6)},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": roof[dom], "peak": peak, "unit": "GB/s",
-                     "frac": roof[dom] / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": roof[dom] / peak, "traffic": NCU_TRAFFIC.get(dom), "peak_source": peak_src,
                      "note": "algorithmic HBM bytes / CUDA-event time per call; refine is bound by the shared-memory pipe and the "
                              "b=1 iter_proj / tracker GN by latency (DESIGN.md section 5); the HBM-bound kernel of this path is the "
                              "graph-sized GN build (bench.py --workload graph)",
@@ -225,6 +225,11 @@ def _kernel_times(be, cfg, sets, steps):
         torch.cuda.synchronize()
         out[name] = a.elapsed_time(b) / steps * 1e3
     return out
+
+
+# dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this workload
+# (profiles/r01c_ncu_full_summary.txt; one 512x384 pair / N=2 E=2 graph): bytes
+NCU_TRAFFIC = {"iter_proj": 11.005e6, "refine": 22.116e6, "gn": 11.490e6}
 
 
 def run_graph(args):

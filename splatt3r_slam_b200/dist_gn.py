@@ -174,7 +174,10 @@ def bench_graph(args, rank, world, local):
                    "sharding": "contiguous edge ranges, one NCCL allreduce of (E,56) fp64 per iteration",
                    "l2": f"per-iteration working set {E * 45.0 * n / world / 1e6:.0f} MB per GPU"},
         "roofline": {"bound": "hbm", "kernel": "gn build (whole iteration incl. solve + allreduce)", "achieved": ach,
-                     "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None, "peak_source": src},
+                     "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                     # build kernel at N=32/E=128 from profiles/r01b_ncu_graph_summary.txt (658.8 MB read per launch;
+                     # keyframe pointmaps are re-used from L2 across edges); other sizes not captured
+                     "traffic": 658.8e6 if (N, E, world) == (32, 128, 1) else None, "peak_source": src},
         "ranks_bit_identical": same, "gpu_launches": args.steps * iters * 4,
         "clocks": sampler.result() if sampler is not None else None,
     }
