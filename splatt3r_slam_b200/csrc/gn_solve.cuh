@@ -484,6 +484,49 @@ __device__ inline void finalize_small(const float *Twc, const int64_t *ii_row, c
   __syncthreads();
 }
 
+// 7x7 SPD solve in fp64 by one thread; H upper triangle row-major (28).  false on a non-positive pivot.
+__device__ inline bool solve7(const double *Hu, const double *g, double *x) {
+  double L[7][7];
+  bool ok = true;
+#pragma unroll
+  for (int a = 0; a < 7; a++) {
+#pragma unroll
+    for (int b = a; b < 7; b++) L[b][a] = Hu[a * 7 - a * (a - 1) / 2 + (b - a)];
+  }
+#pragma unroll
+  for (int j = 0; j < 7; j++) {
+    double d = L[j][j];
+#pragma unroll
+    for (int k = 0; k < j; k++) d -= L[j][k] * L[j][k];
+    ok = ok && (d > 0.0);
+    const double dinv = 1.0 / sqrt(d);
+    L[j][j] = dinv;  // reciprocal diagonal
+#pragma unroll
+    for (int i = j + 1; i < 7; i++) {
+      double s = L[i][j];
+#pragma unroll
+      for (int k = 0; k < j; k++) s -= L[i][k] * L[j][k];
+      L[i][j] = s * dinv;
+    }
+  }
+  double y[7];
+#pragma unroll
+  for (int i = 0; i < 7; i++) {
+    double s = g[i];
+#pragma unroll
+    for (int k = 0; k < i; k++) s -= L[i][k] * y[k];
+    y[i] = s * L[i][i];
+  }
+#pragma unroll
+  for (int i = 6; i >= 0; i--) {
+    double s = y[i];
+#pragma unroll
+    for (int k = i + 1; k < 7; k++) s -= L[k][i] * x[k];
+    x[i] = s * L[i][i];
+  }
+  return ok;
+}
+
 template <int NT>
 __device__ inline void small_tail(float *Twc, const int64_t *ii_row, const int64_t *jj_row,
                                   const double *partials, int S, int E, int N, float delta_thresh, float *dx,
@@ -504,6 +547,46 @@ __device__ inline void small_tail(float *Twc, const int64_t *ii_row, const int64
     __syncthreads();
   }
   if (tid == 0) state->t[1] = gtimer();
+  if (D == 7) {
+    // one free pose (the tracker's N = 2 graph): 28 + 7 sums over the edges, then the unrolled
+    // single-thread 7x7 solve — the generic path below costs 4.4 us per iteration in barriers
+    __shared__ double Hu7[28], g7[7];
+    if (tid < 35) {
+      int a = 0, b = tid;
+      if (tid < 28) {
+        while (b >= 7 - a) { b -= 7 - a; a++; }
+        b += a;
+      }
+      double s = 0.0;
+      for (int e = 0; e < E; e++) {
+        const int i = (int)ii_row[e] - NUM_FIX, j = (int)jj_row[e] - NUM_FIX;
+        if (tid < 28) {
+          const double v = edge_blocks[(size_t)e * 56 + a * 7 + b];
+          if (i == 0) s += v;
+          if (i == 0 && j == 0) s -= 2.0 * v;
+          if (j == 0) s += v;
+        } else {
+          const double v = edge_blocks[(size_t)e * 56 + 49 + (tid - 28)];
+          if (i == 0) s -= v;
+          if (j == 0) s += v;
+        }
+      }
+      if (tid < 28) Hu7[tid] = s;
+      else g7[tid - 28] = s;
+    }
+    __syncthreads();
+    if (tid == 0) {
+      double x[7];
+      fail = solve7(Hu7, g7, x) ? 0 : 1;
+#pragma unroll
+      for (int k = 0; k < 7; k++) xs[k] = x[k];
+      state->t[2] = gtimer();
+    }
+    __syncthreads();
+    finish_update(fail == 0, xs, cols, D, N, Twc, dx, delta_thresh, state);
+    if (tid == 0) state->t[3] = gtimer();
+    return;
+  }
   PackedLower L{Ap};
   for (int t = tid; t < D * D; t += NT) {
     const int r = t / D, c = t % D;

@@ -30,6 +30,7 @@ struct TrackState {      // head of the tracker workspace (256 B)
   double cost, old_cost;
 };
 constexpr int TRACK_NACC = 36;
+constexpr int TRACK_GROUPS = PERSIST_THREADS / TRACK_NACC;  // 14 groups of CTAs in the partial reduction
 
 __device__ __forceinline__ void sim3_mul(const float *A, const float *B, float *C) {  // C = A * B
   float t[3];
@@ -41,49 +42,6 @@ __device__ __forceinline__ void sim3_mul(const float *A, const float *B, float *
   C[5] = a[3] * b[2] + a[0] * b[1] - a[1] * b[0] + a[2] * b[3];
   C[6] = a[3] * b[3] - a[0] * b[0] - a[1] * b[1] - a[2] * b[2];
   C[7] = A[7] * B[7];
-}
-
-// 7x7 SPD solve in fp64 by one thread; H upper triangle row-major (28).  false on a non-positive pivot.
-__device__ inline bool solve7(const double *Hu, const double *g, double *x) {
-  double L[7][7];
-  bool ok = true;
-#pragma unroll
-  for (int a = 0; a < 7; a++) {
-#pragma unroll
-    for (int b = a; b < 7; b++) L[b][a] = Hu[a * 7 - a * (a - 1) / 2 + (b - a)];
-  }
-#pragma unroll
-  for (int j = 0; j < 7; j++) {
-    double d = L[j][j];
-#pragma unroll
-    for (int k = 0; k < j; k++) d -= L[j][k] * L[j][k];
-    ok = ok && (d > 0.0);
-    const double dinv = 1.0 / sqrt(d);
-    L[j][j] = dinv;  // reciprocal diagonal
-#pragma unroll
-    for (int i = j + 1; i < 7; i++) {
-      double s = L[i][j];
-#pragma unroll
-      for (int k = 0; k < j; k++) s -= L[i][k] * L[j][k];
-      L[i][j] = s * dinv;
-    }
-  }
-  double y[7];
-#pragma unroll
-  for (int i = 0; i < 7; i++) {
-    double s = g[i];
-#pragma unroll
-    for (int k = 0; k < i; k++) s -= L[i][k] * y[k];
-    y[i] = s * L[i][i];
-  }
-#pragma unroll
-  for (int i = 6; i >= 0; i--) {
-    double s = y[i];
-#pragma unroll
-    for (int k = i + 1; k < 7; k++) s -= L[k][i] * x[k];
-    x[i] = s * L[i][i];
-  }
-  return ok;
 }
 
 // KIND 0: ray + distance residual (opt_pose_ray_dist_sim3, tracker.py:174-214); B = Xk (n,3).
@@ -235,10 +193,21 @@ track_kernel(const float *__restrict__ Xf, const float *__restrict__ B, const fl
     }
     __syncthreads();
     if (is_last) {
-      __shared__ double tot[TRACK_NACC];
+      // sum of the per-CTA partials in a FIXED order, by the whole CTA: thread (l, grp) adds the CTAs
+      // c = grp (mod TRACK_GROUPS) of accumulator l (independent coalesced loads), thread l then adds the
+      // group sums in order.  (One thread per accumulator walking all 148 partials cost ~11 us per step.)
+      __shared__ double tot[TRACK_NACC], grp_sum[TRACK_GROUPS][TRACK_NACC];
+      if (tid < TRACK_GROUPS * TRACK_NACC) {
+        const int l = tid % TRACK_NACC, grp = tid / TRACK_NACC;
+        double sum = 0.0;
+        for (int c = grp; c < S; c += TRACK_GROUPS) sum += __ldcg(partials + (size_t)c * TRACK_NACC + l);
+        grp_sum[grp][l] = sum;
+      }
+      __syncthreads();
       if (tid < TRACK_NACC) {
         double sum = 0.0;
-        for (int c = 0; c < S; c++) sum += __ldcg(partials + (size_t)c * TRACK_NACC + tid);
+#pragma unroll
+        for (int grp = 0; grp < TRACK_GROUPS; grp++) sum += grp_sum[grp][tid];
         tot[tid] = sum;
       }
       __syncthreads();
