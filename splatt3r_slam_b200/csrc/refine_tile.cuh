@@ -20,7 +20,10 @@
 namespace rtile {
 
 constexpr int TW = 16, TH = 16, THREADS = TW * TH;
-constexpr int BOX_BYTES = 112 * 1024;  // shared-memory box: two CTAs per SM
+#ifndef RT_BOX_KB
+#define RT_BOX_KB 112
+#endif
+constexpr int BOX_BYTES = RT_BOX_KB * 1024;  // shared-memory box: two CTAs per SM at 112 KB
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -107,7 +110,7 @@ __device__ __forceinline__ void scan_column(const __half2 (&q)[FDIM / 2], int u,
 }
 
 template <int FDIM, int RADIUS>
-__global__ void __launch_bounds__(THREADS, 2)
+__global__ void __launch_bounds__(THREADS, RT_BOX_KB > 113 ? 1 : 2)
 refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D21,
                    const int64_t *__restrict__ p1, int64_t *__restrict__ p1_new, int h, int w, int n,
                    int qw, int dilation_max, int lin_out) {

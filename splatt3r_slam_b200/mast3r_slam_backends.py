@@ -14,7 +14,7 @@ import os
 import torch
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_LIB_PATH = os.path.join(_HERE, "libb200slam.so")
+_LIB_PATH = os.environ.get("B200SLAM_LIB") or os.path.join(_HERE, "libb200slam.so")  # override: A/B builds
 
 GN_RAYS, GN_CALIB, GN_POINTS = 0, 1, 2
 
