@@ -174,6 +174,20 @@ int b200slam_gauss_newton_ids(const b200slam_gn_params *prm, float *Twc, const f
                               int n, int max_iter, float delta_thresh, float *dx, void *workspace,
                               size_t workspace_bytes, void *stream);
 
+/* Same loop on the factor graph's ONE-WAY edge lists: the reference doubles every per-edge array with
+ * torch.cat before each solve (FactorGraph.prep_two_way_edges, global_opt.py:104-110: 2.56 MB per edge at
+ * 512x384); here directed edge e < E1 is (ii[e] -> jj[e]) with idx_ii2jj / valid_match_j / Q_ii2jj and edge
+ * E1 + e is (jj[e] -> ii[e]) with idx_jj2ii / valid_match_i / Q_jj2ii, read in place.  Results are
+ * bit-identical to b200slam_gauss_newton_ids on the concatenated arrays.  Workspace:
+ * b200slam_gn_workspace_bytes(N, 2 * E1, n).   */
+int b200slam_gauss_newton_twoway(const b200slam_gn_params *prm, float *Twc, const float *Xs,
+                                 const float *Cs, const float *K, const int64_t *ii, const int64_t *jj,
+                                 const int64_t *idx_ii2jj, const int64_t *idx_jj2ii,
+                                 const uint8_t *valid_match_j, const uint8_t *valid_match_i,
+                                 const float *Q_ii2jj, const float *Q_jj2ii, int N, int E1, int n,
+                                 int max_iter, float delta_thresh, float *dx, void *workspace,
+                                 size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

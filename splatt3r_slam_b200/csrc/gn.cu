@@ -124,9 +124,10 @@ build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__
 
   const float *Xi_base = Xs + (size_t)ix * n * 3, *Xj_base = Xs + (size_t)jx * n * 3;
   const float *Ci_base = Cs + (size_t)ix * n, *Cj_base = Cs + (size_t)jx * n;
-  const int64_t *idx_e = idx + (size_t)e * n;
-  const uint8_t *val_e = valid + (size_t)e * n;
-  const float *Q_e = Q + (size_t)e * n;
+  const bool second = e >= C.E1;
+  const int64_t *idx_e = (second ? C.idx2 : idx) + (size_t)e * n;
+  const uint8_t *val_e = (second ? C.valid2 : valid) + (size_t)e * n;
+  const float *Q_e = (second ? C.Q2 : Q) + (size_t)e * n;
 
   float acc[NACC];
 #pragma unroll

@@ -330,21 +330,14 @@ extern "C" int b200slam_edge_rows(const int64_t *ii, const int64_t *jj, int E, i
   return (int)cudaGetLastError();
 }
 
-extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, const float *Xs,
-                                     const float *Cs, const float *K, const int64_t *ii_row,
-                                     const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
-                                     const float *Q, int N, int E, int n, int max_iter, float delta_thresh,
-                                     float *dx, void *workspace, size_t workspace_bytes, void *stream) {
-  if (bad_args(prm, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, N, E, n, workspace) || !dx || N < 2)
-    return B200SLAM_EINVAL;
-  const Layout L = make_layout(N, E, n);
-  if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
-  cudaStream_t st = (cudaStream_t)stream;
-  char *ws = (char *)workspace;
-  int rc = check_K(prm, K);
-  if (rc) return rc;
-  const BuildConsts C = make_consts(prm, K);
-  rc = (int)cudaMemsetAsync(ws, 0, STATE_BYTES, st);
+namespace b200gn {
+// The Gauss-Newton loop on row-indexed edges (C carries the residual model and, for two-way lists, the
+// second set of per-edge arrays).
+inline int gauss_newton_run(const b200slam_gn_params *prm, const BuildConsts &C, float *Twc, const float *Xs,
+                            const float *Cs, const int64_t *ii_row, const int64_t *jj_row, const int64_t *idx,
+                            const uint8_t *valid, const float *Q, int N, int E, int n, int max_iter,
+                            float delta_thresh, float *dx, char *ws, const Layout &L, cudaStream_t st) {
+  int rc = (int)cudaMemsetAsync(ws, 0, STATE_BYTES, st);
   if (rc) return rc;
   double *eb = reinterpret_cast<double *>(ws + L.edge_blocks);
   const bool fused = 7 * (N - NUM_FIX) <= SMALL_MAX_D && E <= SMALL_MAX_E;
@@ -368,6 +361,22 @@ extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, 
   }
   return 0;
 }
+}  // namespace b200gn
+
+extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, const float *Xs,
+                                     const float *Cs, const float *K, const int64_t *ii_row,
+                                     const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                                     const float *Q, int N, int E, int n, int max_iter, float delta_thresh,
+                                     float *dx, void *workspace, size_t workspace_bytes, void *stream) {
+  if (bad_args(prm, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, N, E, n, workspace) || !dx || N < 2)
+    return B200SLAM_EINVAL;
+  const Layout L = make_layout(N, E, n);
+  if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
+  int rc = check_K(prm, K);
+  if (rc) return rc;
+  return gauss_newton_run(prm, make_consts(prm, K), Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, N, E, n, max_iter,
+                          delta_thresh, dx, (char *)workspace, L, (cudaStream_t)stream);
+}
 
 extern "C" int b200slam_gauss_newton_ids(const b200slam_gn_params *prm, float *Twc, const float *Xs,
                                          const float *Cs, const float *K, const int64_t *ii,
@@ -384,4 +393,42 @@ extern "C" int b200slam_gauss_newton_ids(const b200slam_gn_params *prm, float *T
   if (rc) return rc;
   return b200slam_gauss_newton(prm, Twc, Xs, Cs, K, rows, rows + E, idx, valid, Q, N, E, n, max_iter,
                                delta_thresh, dx, workspace, workspace_bytes, stream);
+}
+
+extern "C" int b200slam_gauss_newton_twoway(const b200slam_gn_params *prm, float *Twc, const float *Xs,
+                                            const float *Cs, const float *K, const int64_t *ii,
+                                            const int64_t *jj, const int64_t *idx_ii2jj,
+                                            const int64_t *idx_jj2ii, const uint8_t *valid_match_j,
+                                            const uint8_t *valid_match_i, const float *Q_ii2jj,
+                                            const float *Q_jj2ii, int N, int E1, int n, int max_iter,
+                                            float delta_thresh, float *dx, void *workspace,
+                                            size_t workspace_bytes, void *stream) {
+  if (E1 < 0 || E1 > 0x3fffffff) return B200SLAM_EINVAL;
+  const int E = 2 * E1;
+  if (bad_args(prm, Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match_j, Q_ii2jj, N, E, n, workspace) || !idx_jj2ii ||
+      !valid_match_i || !Q_jj2ii || !dx || N < 2)
+    return B200SLAM_EINVAL;
+  const Layout L = make_layout(N, E, n);
+  if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  char *ws = (char *)workspace;
+  int rc = check_K(prm, K);
+  if (rc) return rc;
+  // rows[0..2E1) = ranks of cat(ii, jj) = i-rows of the 2*E1 directed edges; their j-rows are the halves swapped
+  int64_t *rows = reinterpret_cast<int64_t *>(ws + L.rows);
+  rc = b200slam_edge_rows(ii, jj, E1, rows, ws + L.first, (size_t)2 * E1, stream);
+  if (rc) return rc;
+  if (E1 > 0) {
+    rc = (int)cudaMemcpyAsync(rows + 2 * (size_t)E1, rows + E1, (size_t)E1 * sizeof(int64_t), cudaMemcpyDeviceToDevice, st);
+    if (rc) return rc;
+    rc = (int)cudaMemcpyAsync(rows + 3 * (size_t)E1, rows, (size_t)E1 * sizeof(int64_t), cudaMemcpyDeviceToDevice, st);
+    if (rc) return rc;
+  }
+  BuildConsts C = make_consts(prm, K);
+  C.E1 = E1;
+  C.idx2 = idx_jj2ii - (size_t)E1 * n;  // so that (idx2 + e * n) addresses row e - E1
+  C.valid2 = valid_match_i - (size_t)E1 * n;
+  C.Q2 = Q_jj2ii - (size_t)E1 * n;
+  return gauss_newton_run(prm, C, Twc, Xs, Cs, rows, rows + 2 * (size_t)E1, idx_ii2jj, valid_match_j, Q_ii2jj, N, E,
+                          n, max_iter, delta_thresh, dx, ws, L, st);
 }

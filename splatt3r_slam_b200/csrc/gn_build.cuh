@@ -94,6 +94,12 @@ struct BuildConsts {
   float fx, fy, cx, cy, z_eps, ulo, uhi, vlo, vhi;
   int width;
   const float *Kptr;  // device (3,3) intrinsics, read by the calib kernel itself (no host sync)
+  // two-way edge lists without the caller's torch.cat (global_opt.py:104-110): directed edges e >= E1 read
+  // their per-edge arrays from the second set (pointers pre-offset by -E1 rows); E1 = INT_MAX: one set only
+  int E1 = 0x7fffffff;
+  const int64_t *idx2 = nullptr;
+  const uint8_t *valid2 = nullptr;
+  const float *Q2 = nullptr;
 };
 
 // One point.  Xi/ci = matched point of keyframe i, Xj/cj = point k of keyframe j.

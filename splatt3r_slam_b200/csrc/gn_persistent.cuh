@@ -53,9 +53,10 @@ gn_persistent_kernel(float *Twc, const float *__restrict__ Xs, const float *__re
   {
     const float *Xi_base = Xs + (size_t)ix * n * 3, *Xj_base = Xs + (size_t)jx * n * 3;
     const float *Ci_base = Cs + (size_t)ix * n, *Cj_base = Cs + (size_t)jx * n;
-    const int64_t *idx_e = idx + (size_t)e * n;
-    const uint8_t *val_e = valid + (size_t)e * n;
-    const float *Q_e = Q + (size_t)e * n;
+    const bool second = e >= C.E1;
+    const int64_t *idx_e = (second ? C.idx2 : idx) + (size_t)e * n;
+    const uint8_t *val_e = (second ? C.valid2 : valid) + (size_t)e * n;
+    const float *Q_e = (second ? C.Q2 : Q) + (size_t)e * n;
     for (int g = g_begin + tid; g < g_end; g += PERSIST_THREADS) {
       const uint32_t vm4 = __ldg(reinterpret_cast<const uint32_t *>(val_e) + g);
       const longlong2 ia = __ldg(reinterpret_cast<const longlong2 *>(idx_e) + 2 * g);

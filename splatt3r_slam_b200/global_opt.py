@@ -1,0 +1,72 @@
+"""Host-side mirror of the Gauss-Newton glue of the reference's `FactorGraph`
+(`splatt3r_slam/global_opt.py:101-213`: get_unique_kf_idx, prep_two_way_edges, get_poses_points,
+solve_GN_rays, solve_GN_calib) on plain tensors — and the device-resident variant SURVEY.md section 8f rank 3
+asks for:
+
+  * the reference stacks the pointmaps / confidences / poses of all N keyframes into fresh tensors for
+    every solve (3.1 MB per keyframe at 512x384) — `keyframe_views` returns zero-copy views of the shared
+    keyframe buffers when the graph's keyframe ids are 0..N-1 (the normal case: every keyframe has an edge
+    to its predecessor) and gathers only otherwise;
+  * the reference concatenates every per-edge array with its reverse (2.56 MB per edge) — the backend's
+    two-way entry reads the one-way lists in place.
+
+`graph` is any object with the reference FactorGraph's tensor fields (ii, jj, idx_ii2jj, idx_jj2ii,
+valid_match_j, valid_match_i, Q_ii2jj, Q_jj2ii); `X_buf (cap,n,3)`, `C_buf (cap,n,1)`, `T_buf (cap,8)` are the
+keyframe buffers (reference frame.py:266-268 SharedKeyframes.X / .C / .T_WC).  Poses are written back into
+`T_buf` like `SharedKeyframes.update_T_WCs` (global_opt.py:158)."""
+import torch
+
+DEFAULT_CFG = dict(pin=1, C_conf=0.0, Q_conf=1.5, max_iters=10, sigma_ray=0.003, sigma_dist=10.0, sigma_pixel=1.0,
+                   sigma_depth=10.0, sigma_point=0.05, delta_norm=1e-8, pixel_border=-10, depth_eps=1e-6)
+
+
+def get_unique_kf_idx(graph):
+    return torch.unique(torch.cat([graph.ii, graph.jj]), sorted=True)
+
+
+def prep_two_way_edges(graph):
+    """global_opt.py:104-110, kept for callers that want the concatenated lists."""
+    return (torch.cat((graph.ii, graph.jj)), torch.cat((graph.jj, graph.ii)),
+            torch.cat((graph.idx_ii2jj, graph.idx_jj2ii)), torch.cat((graph.valid_match_j, graph.valid_match_i)),
+            torch.cat((graph.Q_ii2jj, graph.Q_jj2ii)))
+
+
+def keyframe_views(X_buf, C_buf, T_buf, unique_kf_idx):
+    """(Xs, Cs, poses, zero_copy): rows `unique_kf_idx` of the buffers — views when the ids are 0..N-1."""
+    N = unique_kf_idx.numel()
+    contiguous_ids = bool((unique_kf_idx[0] == 0) & (unique_kf_idx[-1] == N - 1))  # sorted + distinct => 0..N-1
+    if contiguous_ids:
+        return X_buf[:N], C_buf[:N], T_buf[:N], True
+    return (X_buf.index_select(0, unique_kf_idx), C_buf.index_select(0, unique_kf_idx),
+            T_buf.index_select(0, unique_kf_idx), False)
+
+
+def _solve(kind_args, graph, X_buf, C_buf, T_buf, K, cfg, backend):
+    cfg = DEFAULT_CFG if cfg is None else cfg
+    if backend is None:
+        from . import mast3r_slam_backends as backend
+    pin = cfg["pin"]
+    unique_kf_idx = get_unique_kf_idx(graph)
+    if unique_kf_idx.numel() <= pin:
+        return None
+    Xs, Cs, poses, zero_copy = keyframe_views(X_buf, C_buf, T_buf, unique_kf_idx)
+    prm = backend.make_params(*kind_args(cfg))
+    (dx,) = backend.gauss_newton_twoway(prm, poses, Xs, Cs, K, graph.ii, graph.jj, graph.idx_ii2jj, graph.idx_jj2ii,
+                                        graph.valid_match_j, graph.valid_match_i, graph.Q_ii2jj, graph.Q_jj2ii,
+                                        cfg["max_iters"], cfg["delta_norm"])
+    if not zero_copy:  # update_T_WCs(T_WCs[pin:], unique_kf_idx[pin:])
+        T_buf.index_copy_(0, unique_kf_idx[pin:], poses[pin:])
+    return dx
+
+
+def solve_GN_rays(graph, X_buf, C_buf, T_buf, cfg=None, backend=None):
+    """global_opt.py:121-158."""
+    return _solve(lambda c: (0, c["sigma_ray"], c["sigma_dist"], c["C_conf"], c["Q_conf"]), graph, X_buf, C_buf, T_buf,
+                  None, cfg, backend)
+
+
+def solve_GN_calib(graph, X_buf, C_buf, T_buf, K, img_size, cfg=None, backend=None):
+    """global_opt.py:160-213.  `X_buf` must already hold ray-constrained points (constrain_points_to_ray, :172)."""
+    h, w = img_size
+    return _solve(lambda c: (1, c["sigma_pixel"], c["sigma_depth"], c["C_conf"], c["Q_conf"], h, w, c["pixel_border"],
+                             c["depth_eps"]), graph, X_buf, C_buf, T_buf, K, cfg, backend)

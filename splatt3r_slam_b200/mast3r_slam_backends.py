@@ -49,6 +49,7 @@ def _load():
     lib.b200slam_gauss_newton.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_gauss_newton_ids.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_edge_rows.argtypes = [vp, vp, i, vp, vp, sz, vp]
+    lib.b200slam_gauss_newton_twoway.argtypes = [P] + [vp] * 12 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_track_workspace_bytes.argtypes = []
     lib.b200slam_track_workspace_bytes.restype = sz
     lib.b200slam_track_ray_dist.argtypes = [vp] * 8 + [i, f, f, f, i, f, f, vp, sz, vp]
@@ -60,7 +61,7 @@ def _load():
     lib.b200slam_match.argtypes = [vp] * 4 + [i] + [vp] * 3 + [i] * 5 + [f, f, f, i, i, vp, sz, vp]
     for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "gn_build_blocks",
                  "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gauss_newton",
-                 "gauss_newton_ids", "edge_rows", "match", "track_ray_dist", "track_calib", "track_status"):
+                 "gauss_newton_ids", "gauss_newton_twoway", "edge_rows", "match", "track_ray_dist", "track_calib", "track_status"):
         getattr(lib, "b200slam_" + name).restype = i
     return lib
 
@@ -329,6 +330,34 @@ def gauss_newton_points(Twc, Xs, Cs, ii, jj, idx_ii2jj, valid_match, Q, sigma_po
                         max_iter, delta_thresh):
     prm = GNParams(GN_POINTS, sigma_point, 1.0, C_thresh, Q_thresh, 0, 0, 0, 0.0)
     return _gauss_newton(prm, Twc, Xs, Cs, None, ii, jj, idx_ii2jj, valid_match, Q, max_iter, delta_thresh)
+
+
+def gauss_newton_twoway(prm, Twc, Xs, Cs, K, ii, jj, idx_ii2jj, idx_jj2ii, valid_match_j, valid_match_i, Q_ii2jj,
+                        Q_jj2ii, max_iter, delta_thresh):
+    """The GN loop on the factor graph's ONE-WAY edge lists (reference FactorGraph fields, global_opt.py:21-29):
+    same result as `gauss_newton_*` on `prep_two_way_edges()`'s concatenations (global_opt.py:104-110), without
+    making them.  prm: `make_params(...)`.  Updates Twc in place; returns [dx]."""
+    _contig(Twc=Twc, Xs=Xs, Cs=Cs, ii=ii, jj=jj, idx_ii2jj=idx_ii2jj, idx_jj2ii=idx_jj2ii, valid_match_j=valid_match_j,
+            valid_match_i=valid_match_i, Q_ii2jj=Q_ii2jj, Q_jj2ii=Q_jj2ii)
+    if K is not None:
+        _contig(K=K)
+    N, n, E1 = Xs.shape[0], Xs.shape[1], ii.shape[0]
+    ptrs = (_cuda(Twc, torch.float32, "Twc"), _cuda(Xs, torch.float32, "Xs"), _cuda(Cs, torch.float32, "Cs"),
+            (_cuda(K, torch.float32, "K") if K is not None else None), _cuda(ii, torch.int64, "ii"),
+            _cuda(jj, torch.int64, "jj"), _cuda(idx_ii2jj, torch.int64, "idx_ii2jj"),
+            _cuda(idx_jj2ii, torch.int64, "idx_jj2ii"), _cuda(valid_match_j, torch.bool, "valid_match_j"),
+            _cuda(valid_match_i, torch.bool, "valid_match_i"), _cuda(Q_ii2jj, torch.float32, "Q_ii2jj"),
+            _cuda(Q_jj2ii, torch.float32, "Q_jj2ii"))
+    with _guard(Twc):
+        dx = torch.zeros((max(N - 1, 0), 7), dtype=torch.float32, device=Twc.device)
+        if max_iter <= 0 or N < 2 or E1 == 0:
+            return [dx]
+        nbytes = _lib.b200slam_gn_workspace_bytes(N, 2 * E1, n)
+        ws = _workspace(Twc.device, nbytes)
+        _check(_lib.b200slam_gauss_newton_twoway(
+            ctypes.byref(prm), *ptrs, N, E1, n, int(max_iter), float(delta_thresh), dx.data_ptr(), ws.data_ptr(), nbytes,
+            _stream(Twc)), "gauss_newton_twoway")
+    return [dx]
 
 
 # ---- extras beyond the reference module (used by tests, bench and the multi-GPU driver) ----------
