@@ -2,7 +2,7 @@
 // windows in shared memory.  Same arithmetic and scan order as refine_f16_kernel (bit-exact with
 // matching_kernels.cu:24-80); different data path:
 //
-//   A CTA owns a 16x16 tile of query pixels.  At every dilation level the CTA reduces the bounding
+//   A CTA owns a TW x TH (32x16) tile of query pixels.  At every dilation level the CTA reduces the bounding
 //   box of its queries' current centres, grows it by the level's reach (radius*d), clips it to the
 //   image and lets ONE thread issue one `cp.async.bulk` (UBLKCP) per box row: (box_w * fdim * 2)
 //   contiguous bytes of D11 -> shared memory, completion signalled on an mbarrier.  Every query
@@ -19,11 +19,20 @@
 
 namespace rtile {
 
-constexpr int TW = 16, TH = 16, THREADS = TW * TH;
-#ifndef RT_BOX_KB
-#define RT_BOX_KB 112
+// Query tile and box size (build macros for A/B runs).  Measured on B200, 512x384 pairs:
+//   16x16 queries, 112 KB box, 2 CTAs/SM   265 us  (the dilation-5 box of a 16x16 tile is 48x48 px = 110.6 KB: any
+//                                                   spread of the match centres overflows it, and the queries
+//                                                   left outside take the global-memory path)
+//   16x16 queries, 224 KB box, 1 CTA/SM    257 us  (no overflow, half the warps)
+//   32x16 queries, 224 KB box, 1 CTA/SM    242 us  (no overflow, same 16 warps per SM)   <- default
+#ifndef RT_TW
+#define RT_TW 32
 #endif
-constexpr int BOX_BYTES = RT_BOX_KB * 1024;  // shared-memory box: two CTAs per SM at 112 KB
+#ifndef RT_BOX_KB
+#define RT_BOX_KB 224
+#endif
+constexpr int TW = RT_TW, TH = 16, THREADS = TW * TH;
+constexpr int BOX_BYTES = RT_BOX_KB * 1024;  // shared-memory box per CTA
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
