@@ -116,7 +116,7 @@ __device__ __forceinline__ bool iter_proj_core(const float *__restrict__ img, in
 }
 
 // One thread per query pixel; planes (9, h*w) of batch row blockIdx.y.
-__global__ void __launch_bounds__(IP_THREADS)
+__global__ void __launch_bounds__(IP_THREADS, IP_MIN_CTAS)
 iter_proj_kernel(const float *__restrict__ planes, const float *__restrict__ pts,
                  const float *__restrict__ p_init, float *__restrict__ p_new,
                  uint8_t *__restrict__ converged, int h, int w, int n, int max_iter,

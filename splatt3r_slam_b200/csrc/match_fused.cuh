@@ -79,7 +79,7 @@ prep_planes_kernel(const float *__restrict__ X11, float *__restrict__ planes, in
 }
 
 // One thread per query pixel of view 2 (n == h*w).  p1 (b,n,2) int64 = truncated pixel, valid (b,n).
-__global__ void __launch_bounds__(IP_THREADS)
+__global__ void __launch_bounds__(IP_THREADS, IP_MIN_CTAS)
 match_proj_kernel(const float *__restrict__ planes, const float *__restrict__ X11,
                   const float *__restrict__ X21, const int64_t *__restrict__ idx_init,
                   int64_t *__restrict__ p1, uint8_t *__restrict__ valid, int h, int w, int max_iter,
