@@ -128,7 +128,8 @@ def run_tracker(args):
         b = i % n_buf
         d = dbuf[b]
         comp_stream.wait_event(copied[b])
-        idx, valid = matching.match(d["X11"], d["X21"], d["D11"], d["D21"], backend=be)
+        # the match driver's single fused entry (b200slam_match: same bits as glue + iter_proj + refine_matches)
+        idx, valid = matching.match(d["X11"], d["X21"], d["D11"], d["D21"], backend=be, fused=True)
         be.gauss_newton_rays(d["Twc"], d["Xs"], d["Cs"], d["ii"], d["jj"], d["idx_ii2jj"], d["valid_match"], d["Q"],
                              GN["sigma_ray"], GN["sigma_dist"], GN["C_thresh"], GN["Q_thresh"], GN["iters"], 0.0)
         o = outs[b]
@@ -173,7 +174,9 @@ def run_tracker(args):
                    "l2": f"{n_sets} rotating input sets of ~56 MB (> 126 MB L2)", "ranks": "independent pairs per rank, no collective"},
         "e2e": {"value": world * N_PIX * args.steps / (ms_e2e * 1e-3), "unit": "px/s", "h2d_bytes_per_step": h2d,
                 "d2h_bytes_per_step": d2h, "ms_per_step": ms_e2e / args.steps,
-                "pipeline": "H2D of step i+1 overlaps the kernels of step i (2 device buffers, copy stream + events)"},
+                "pipeline": "H2D of step i+1 overlaps the kernels of step i (2 device buffers, copy stream + events)",
+                "api": "matching.match(X11, X21, D11, D21, fused=True) [f32 pointmaps + f32 descriptors from host] + "
+                       "mast3r_slam_backends.gauss_newton_rays"},
         # per step: repack_planar + iter_proj + refine_tile + first_occurrence + rank + ONE persistent GN kernel
         # (all 10 iterations; cooperative launch) = 6 launches of this library's kernels
         "gpu_launches": args.steps * 6,

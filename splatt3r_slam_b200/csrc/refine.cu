@@ -180,7 +180,9 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
   const int reach = radius * dilation_max;
   if (fdim == 24 && aligned && radius == 3 && n == h * w && dilation_max >= 1 && w >= rtile::TW + 2 * reach + 2) {
     const int tiles = ((w + rtile::TW - 1) / rtile::TW) * ((h + rtile::TH - 1) / rtile::TH);
-    const long long nominal = (long long)(rtile::TW + 2 * reach + 2) * (rtile::TH + 2 * reach + 2) * fdim * 2;
+    // a level whose full nominal box does not fit is scanned in two column passes of half the reach in x
+    long long nominal = (long long)(rtile::TW + 2 * reach + rtile::SLACK) * (rtile::TH + 2 * reach + rtile::SLACK) * fdim * 2;
+    if (nominal > rtile::BOX_BYTES) nominal = (long long)(rtile::TW + reach + 2) * (rtile::TH + 2 * reach + 2) * fdim * 2;
     if (nominal <= rtile::BOX_BYTES) {
       static bool attr_set = false;
       if (!attr_set) {

@@ -28,10 +28,19 @@ namespace rtile {
 #ifndef RT_TW
 #define RT_TW 32
 #endif
+#ifndef RT_TH
+#define RT_TH 16
+#endif
 #ifndef RT_BOX_KB
 #define RT_BOX_KB 224
 #endif
-constexpr int TW = RT_TW, TH = 16, THREADS = TW * TH;
+#ifndef RT_SLACK
+#define RT_SLACK 2  // spread of the match centres (px) a level's box must absorb before the level is split in two
+#endif
+#ifndef RT_PERMUTE
+#define RT_PERMUTE 1  // re-deal the queries of a warp to its lanes per level so that quarter-warps hit distinct banks
+#endif
+constexpr int TW = RT_TW, TH = RT_TH, THREADS = TW * TH, SLACK = RT_SLACK;
 constexpr int BOX_BYTES = RT_BOX_KB * 1024;  // shared-memory box per CTA
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -162,12 +171,28 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
   int u_new = u0, v_new = v0;
   float max_score = 0.0f;
   uint32_t parity = 0;
+  // queries that could never hit the image keep their input pixel verbatim (64-bit): written here, so
+  // that only (centre, score, descriptor, output slot) travel with a query when lanes are re-dealt
+  if (active && !can_hit) {
+    if (lin_out) p1_new[bq] = pin.x + (long long)w * pin.y;
+    else reinterpret_cast<longlong2 *>(p1_new)[bq] = pin;
+  }
+  bool live = active && can_hit;
+  int qout = (int)qlin;  // output slot of the query this lane currently holds (n < 2^31 on this path)
+#if RT_PERMUTE
+  __shared__ int lane_of_slot[THREADS / 32][32];
+#endif
   __syncthreads();  // mbarrier initialised
 
-  for (int d = dilation_max; d > 0; d--) {
+  for (int pass = 0, d = dilation_max; d > 0; pass++) {
     const int rd = RADIUS * d;
+    // A level whose nominal box (tile + reach + SLACK px) exceeds the shared-memory box is
+    // scanned in two passes of candidate columns, i <= 0 then i > 0 (same i-outer scan order), each
+    // with a box of half the reach in x.  With the default 224 KB box no level splits.
+    const bool split = (TW + 2 * rd + SLACK) * (TH + 2 * rd + SLACK) > MAX_PX;
+    const int ilo = split && pass ? d : -rd, ihi = split && !pass ? 0 : rd;
     // ---- bounding box of the centres of this tile (queries that can hit the image only) --------
-    const bool part = active && can_hit;
+    const bool part = live;
     int vals[6] = {part ? u0 : (1 << 29), part ? -u0 : (1 << 29), part ? v0 : (1 << 29),
                    part ? -v0 : (1 << 29), part ? u0 : 0, part ? v0 : 0};
     const unsigned cnt_w = __popc(__ballot_sync(0xffffffffu, part));
@@ -191,13 +216,13 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
       }
       Box b{0, 0, 0, 0};
       if (c > 0) {
-        int x0 = max(umin - rd, 0), x1 = min(-numax + rd, w - 1);
+        int x0 = max(umin + ilo, 0), x1 = min(-numax + ihi, w - 1);
         int y0 = max(vmin - rd, 0), y1 = min(-nvmax + rd, h - 1);
         if (x1 >= x0 && y1 >= y0) {
           if ((x1 - x0 + 1) * (y1 - y0 + 1) > MAX_PX) {
             // incoherent tile: keep a box of the nominal size around the mean centre
-            const int side_x = min(TW + 2 * rd + 2, w), side_y = min(min(TH + 2 * rd + 2, h), MAX_PX / side_x);
-            const int cx = su / c, cy = sv / c;
+            const int side_x = min(TW + ihi - ilo + 2, w), side_y = min(min(TH + 2 * rd + 2, h), MAX_PX / side_x);
+            const int cx = su / c + (ilo + ihi) / 2, cy = sv / c;
             x0 = min(max(cx - side_x / 2, 0), w - side_x); x1 = x0 + side_x - 1;
             y0 = min(max(cy - side_y / 2, 0), h - side_y); y1 = y0 + side_y - 1;
           }
@@ -220,14 +245,53 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
       mbar_wait(&bar, parity);
       parity ^= 1u;
     }
-    if (active && can_hit) {
+#if RT_PERMUTE
+    // Candidate (i, j) of a query sits at box pixel pix0 + j*bw + i, and a 16-byte chunk of pixel p lies in
+    // bank group (3p + chunk) mod 8: the 8 lanes of a quarter-warp (one LDS.128 phase) are conflict-free
+    // for ALL candidates of the level iff their pix0 differ mod 8.  The first level's centres are
+    // adjacent pixels (conflict-free as dealt); afterwards they scatter (2.3 wavefronts per phase
+    // measured), so the warp re-deals its 32 queries: the k-th query of residue class r goes to lane
+    // 8k + r, the rest (5th+ of a class, dead queries) fill the empty slots from the top quarter down.
+    if (d < dilation_max && !(split && pass)) {
+      const unsigned lt = (1u << lane) - 1u;
+      const int cls = live ? (((v0 - b.y0) * b.bw + (u0 - b.x0)) & 7) : 8;
+      int n_slot = 0, rank = 0;
+#pragma unroll
+      for (int r = 0; r < 8; r++) {
+        const unsigned m = __ballot_sync(0xffffffffu, cls == r);
+        if ((lane & 7) == r) n_slot = __popc(m);
+        if (cls == r) rank = __popc(m & lt);
+      }
+      const unsigned empty = __ballot_sync(0xffffffffu, n_slot <= (lane >> 3));  // slot 8k + r is empty iff n_r <= k
+      const bool spare = cls == 8 || rank >= 4;
+      const unsigned spares = __ballot_sync(0xffffffffu, spare);
+      const int dest = spare ? (int)__fns(empty, 31, -(__popc(spares & lt) + 1)) : (rank << 3 | cls);
+      lane_of_slot[warp][dest] = lane;
+      __syncwarp();
+      const int src = lane_of_slot[warp][lane];
+      __syncwarp();
+#pragma unroll
+      for (int k = 0; k < FDIM / 2; k++) {
+        const unsigned x = __shfl_sync(0xffffffffu, *reinterpret_cast<unsigned *>(&q[k]), src);
+        q[k] = *reinterpret_cast<const __half2 *>(&x);
+      }
+      u0 = __shfl_sync(0xffffffffu, u0, src);
+      v0 = __shfl_sync(0xffffffffu, v0, src);
+      max_score = __shfl_sync(0xffffffffu, max_score, src);
+      qout = __shfl_sync(0xffffffffu, qout, src);
+      live = __shfl_sync(0xffffffffu, (int)live, src) != 0;
+      u_new = u0;
+      v_new = v0;
+    }
+#endif
+    if (live) {
       // window clipped to the image must lie inside the staged box to use shared memory
-      const int wx0 = max(u0 - rd, 0), wx1 = min(u0 + rd, w - 1), wy0 = max(v0 - rd, 0), wy1 = min(v0 + rd, h - 1);
+      const int wx0 = max(u0 + ilo, 0), wx1 = min(u0 + ihi, w - 1), wy0 = max(v0 - rd, 0), wy1 = min(v0 + rd, h - 1);
       const bool in_box = staged && wx0 >= b.x0 && wx1 < b.x0 + b.bw && wy0 >= b.y0 && wy1 < b.y0 + b.bh;
       if (wx0 <= wx1 && wy0 <= wy1) {
         if (in_box) {
           const uint4 *base = reinterpret_cast<const uint4 *>(box_mem);
-          for (int i = -rd; i <= rd; i += d) {
+          for (int i = ilo; i <= ihi; i += d) {
             const int u = u0 + i;
             if (u < 0 || u >= w) continue;
             const int col = (u - b.x0) * (FDIM / 8);
@@ -236,7 +300,7 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
           }
         } else {
           const uint4 *base = reinterpret_cast<const uint4 *>(img);
-          for (int i = -rd; i <= rd; i += d) {
+          for (int i = ilo; i <= ihi; i += d) {
             const int u = u0 + i;
             if (u < 0 || u >= w) continue;
             auto load = [&](int v, int ch) { return __ldg(base + ((size_t)v * w + u) * (FDIM / 8) + ch); };
@@ -245,14 +309,16 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
         }
       }
     }
+    if (split && !pass) continue;  // second half of this level next, same centres
     u0 = u_new;
     v0 = v_new;
+    d--;
+    pass = -1;
   }
-  if (active) {
-    // queries that could never hit the image keep their input pixel verbatim (64-bit)
-    const longlong2 out = can_hit ? make_longlong2(u_new, v_new) : pin;
-    if (lin_out) p1_new[bq] = out.x + (long long)w * out.y;  // pixel_to_lin (matching.py:13-15) folded in
-    else reinterpret_cast<longlong2 *>(p1_new)[bq] = out;
+  if (live) {
+    const size_t bo = (size_t)blockIdx.y * n + qout;
+    if (lin_out) p1_new[bo] = u_new + (long long)w * v_new;  // pixel_to_lin (matching.py:13-15) folded in
+    else reinterpret_cast<longlong2 *>(p1_new)[bo] = make_longlong2(u_new, v_new);
   }
 }
 
