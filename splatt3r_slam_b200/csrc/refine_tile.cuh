@@ -37,6 +37,12 @@ namespace rtile {
 #ifndef RT_SLACK
 #define RT_SLACK 2  // spread of the match centres (px) a level's box must absorb before the level is split in two
 #endif
+#ifndef RT_ISSUE_LANES
+#define RT_ISSUE_LANES 32
+#endif
+#ifndef RT_PERMUTE_FIRST
+#define RT_PERMUTE_FIRST 0  // re-deal at the first (coarsest) level too
+#endif
 #ifndef RT_PERMUTE
 #define RT_PERMUTE 1  // re-deal the queries of a warp to its lanes per level so that quarter-warps hit distinct banks
 #endif
@@ -134,8 +140,7 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
                    int qw, int dilation_max, int lin_out) {
   extern __shared__ __align__(128) unsigned char box_mem[];
   __shared__ uint64_t bar;
-  __shared__ int red[THREADS / 32][6];
-  __shared__ Box sbox;
+  __shared__ int red[2][THREADS / 32][8];
   constexpr int PIX_BYTES = FDIM * 2;
   constexpr int MAX_PX = BOX_BYTES / PIX_BYTES;
 
@@ -171,6 +176,7 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
   int u_new = u0, v_new = v0;
   float max_score = 0.0f;
   uint32_t parity = 0;
+  int buf = 0;
   // queries that could never hit the image keep their input pixel verbatim (64-bit): written here, so
   // that only (centre, score, descriptor, output slot) travel with a query when lanes are re-dealt
   if (active && !can_hit) {
@@ -180,7 +186,7 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
   bool live = active && can_hit;
   int qout = (int)qlin;  // output slot of the query this lane currently holds (n < 2^31 on this path)
 #if RT_PERMUTE
-  __shared__ int lane_of_slot[THREADS / 32][32];
+  __shared__ unsigned char lane_of_slot[THREADS / 32][32];
 #endif
   __syncthreads();  // mbarrier initialised
 
@@ -192,29 +198,34 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
     const bool split = (TW + 2 * rd + SLACK) * (TH + 2 * rd + SLACK) > MAX_PX;
     const int ilo = split && pass ? d : -rd, ihi = split && !pass ? 0 : rd;
     // ---- bounding box of the centres of this tile (queries that can hit the image only) --------
+    // One block barrier per pass: every warp leaves its partial box in shared memory, and after the
+    // barrier EVERY warp reduces the partials itself (shuffles), so nobody waits for an elected thread;
+    // warp 0 then issues the bulk copies, one box row per lane.  `red` is double-buffered by pass: a
+    // fast warp writes the next pass's partials while a slow one may still be reading this pass's.
     const bool part = live;
-    int vals[6] = {part ? u0 : (1 << 29), part ? -u0 : (1 << 29), part ? v0 : (1 << 29),
-                   part ? -v0 : (1 << 29), part ? u0 : 0, part ? v0 : 0};
-    const unsigned cnt_w = __popc(__ballot_sync(0xffffffffu, part));
+    int vals[7] = {part ? u0 : (1 << 29), part ? -u0 : (1 << 29), part ? v0 : (1 << 29),
+                   part ? -v0 : (1 << 29), part ? u0 : 0, part ? v0 : 0, part ? 1 : 0};
 #pragma unroll
     for (int k = 0; k < 4; k++) vals[k] = __reduce_min_sync(0xffffffffu, vals[k]);
-    vals[4] = __reduce_add_sync(0xffffffffu, vals[4]);
-    vals[5] = __reduce_add_sync(0xffffffffu, vals[5]);
+#pragma unroll
+    for (int k = 4; k < 7; k++) vals[k] = __reduce_add_sync(0xffffffffu, vals[k]);
+    int(*redp)[8] = red[buf];
+    buf ^= 1;
     if (lane == 0) {
 #pragma unroll
-      for (int k = 0; k < 6; k++) red[warp][k] = vals[k];
+      for (int k = 0; k < 7; k++) redp[warp][k] = vals[k];
     }
-    __shared__ int cnt[THREADS / 32];
-    if (lane == 0) cnt[warp] = (int)cnt_w;
-    __syncthreads();  // also: every thread has finished reading the previous level's box
-    if (tid == 0) {
-      int umin = 1 << 29, numax = 1 << 29, vmin = 1 << 29, nvmax = 1 << 29, su = 0, sv = 0, c = 0;
-      for (int k = 0; k < THREADS / 32; k++) {
-        umin = min(umin, red[k][0]); numax = min(numax, red[k][1]);
-        vmin = min(vmin, red[k][2]); nvmax = min(nvmax, red[k][3]);
-        su += red[k][4]; sv += red[k][5]; c += cnt[k];
-      }
-      Box b{0, 0, 0, 0};
+    __syncthreads();  // also: every thread has finished reading the previous pass's box
+    {
+      const bool has = lane < THREADS / 32;
+#pragma unroll
+      for (int k = 0; k < 4; k++) vals[k] = __reduce_min_sync(0xffffffffu, has ? redp[lane][k] : (1 << 29));
+#pragma unroll
+      for (int k = 4; k < 7; k++) vals[k] = __reduce_add_sync(0xffffffffu, has ? redp[lane][k] : 0);
+    }
+    Box b{0, 0, 0, 0};
+    {
+      const int umin = vals[0], numax = vals[1], vmin = vals[2], nvmax = vals[3], su = vals[4], sv = vals[5], c = vals[6];
       if (c > 0) {
         int x0 = max(umin + ilo, 0), x1 = min(-numax + ihi, w - 1);
         int y0 = max(vmin - rd, 0), y1 = min(-nvmax + rd, h - 1);
@@ -229,22 +240,17 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
           b = Box{x0, y0, x1 - x0 + 1, y1 - y0 + 1};
         }
       }
-      sbox = b;
-      if (b.bw * b.bh > 0) {
-        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic reads -> async writes
-        const uint32_t row_bytes = (uint32_t)b.bw * PIX_BYTES;
-        mbar_expect_tx(&bar, row_bytes * (uint32_t)b.bh);
-        for (int r = 0; r < b.bh; r++)
+    }
+    if (warp == 0 && b.bw * b.bh > 0) {
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");  // generic reads -> async writes
+      const uint32_t row_bytes = (uint32_t)b.bw * PIX_BYTES;
+      if (lane == 0) mbar_expect_tx(&bar, row_bytes * (uint32_t)b.bh);
+      __syncwarp();
+      if (lane < RT_ISSUE_LANES)
+        for (int r = lane; r < b.bh; r += RT_ISSUE_LANES)
           bulk_g2s(box_mem + (size_t)r * row_bytes, img + ((size_t)(b.y0 + r) * w + b.x0) * FDIM, row_bytes, &bar);
-      }
     }
-    __syncthreads();
-    const Box b = sbox;
     const bool staged = b.bw * b.bh > 0;
-    if (staged) {
-      mbar_wait(&bar, parity);
-      parity ^= 1u;
-    }
 #if RT_PERMUTE
     // Candidate (i, j) of a query sits at box pixel pix0 + j*bw + i, and a 16-byte chunk of pixel p lies in
     // bank group (3p + chunk) mod 8: the 8 lanes of a quarter-warp (one LDS.128 phase) are conflict-free
@@ -252,7 +258,7 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
     // adjacent pixels (conflict-free as dealt); afterwards they scatter (2.3 wavefronts per phase
     // measured), so the warp re-deals its 32 queries: the k-th query of residue class r goes to lane
     // 8k + r, the rest (5th+ of a class, dead queries) fill the empty slots from the top quarter down.
-    if (d < dilation_max && !(split && pass)) {
+    if ((RT_PERMUTE_FIRST || d < dilation_max) && !(split && pass)) {
       const unsigned lt = (1u << lane) - 1u;
       const int cls = live ? (((v0 - b.y0) * b.bw + (u0 - b.x0)) & 7) : 8;
       int n_slot = 0, rank = 0;
@@ -266,7 +272,7 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
       const bool spare = cls == 8 || rank >= 4;
       const unsigned spares = __ballot_sync(0xffffffffu, spare);
       const int dest = spare ? (int)__fns(empty, 31, -(__popc(spares & lt) + 1)) : (rank << 3 | cls);
-      lane_of_slot[warp][dest] = lane;
+      lane_of_slot[warp][dest] = (unsigned char)lane;
       __syncwarp();
       const int src = lane_of_slot[warp][lane];
       __syncwarp();
@@ -284,6 +290,10 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
       v_new = v0;
     }
 #endif
+    if (staged) {  // (the re-deal above needs only the box geometry: it overlaps the copy)
+      mbar_wait(&bar, parity);
+      parity ^= 1u;
+    }
     if (live) {
       // window clipped to the image must lie inside the staged box to use shared memory
       const int wx0 = max(u0 + ilo, 0), wx1 = min(u0 + ihi, w - 1), wy0 = max(v0 - rd, 0), wy1 = min(v0 + rd, h - 1);
