@@ -179,7 +179,23 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
   // (n == h*w, as in matching.py:79-85), radius 3, and the nominal box of the coarsest level fits.
   const int reach = radius * dilation_max;
   if (fdim == 24 && aligned && radius == 3 && n == h * w && dilation_max >= 1 && w >= rtile::TW + 2 * reach + 2) {
-    const int tiles = ((w + rtile::TW - 1) / rtile::TW) * ((h + rtile::TH - 1) / rtile::TH);
+    // band count: fewest waves x rows-per-tile (time of a tile ~ its query rows); see refine_tile.cuh
+    static int n_sm = 0;
+    if (!n_sm) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      if (cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sm < 1) n_sm = 148;
+    }
+    const int tiles_x = (w + rtile::TW - 1) / rtile::TW, bands_min = (h + rtile::TH - 1) / rtile::TH;
+    int bands = bands_min;
+#ifndef RT_NO_BANDS
+    long long best = -1;
+    for (int nb = bands_min; nb <= bands_min + bands_min / 2 && nb <= h; nb++) {
+      const long long waves = ((long long)tiles_x * nb * b + n_sm - 1) / n_sm, rows = (h + nb - 1) / nb;
+      if (best < 0 || waves * rows < best) { best = waves * rows; bands = nb; }
+    }
+#endif
+    const int tiles = tiles_x * bands;
     // a level whose full nominal box does not fit is scanned in two column passes of half the reach in x
     long long nominal = (long long)(rtile::TW + 2 * reach + rtile::SLACK) * (rtile::TH + 2 * reach + rtile::SLACK) * fdim * 2;
     if (nominal > rtile::BOX_BYTES) nominal = (long long)(rtile::TW + reach + 2) * (rtile::TH + 2 * reach + 2) * fdim * 2;
@@ -191,7 +207,7 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
         attr_set = true;
       }
       rtile::refine_tile_kernel<24, 3><<<dim3(tiles, b), rtile::THREADS, rtile::BOX_BYTES, st>>>(
-          a, q, p1, p1_new, h, w, n, w, dilation_max, lin_out);
+          a, q, p1, p1_new, h, w, n, w, bands, dilation_max, lin_out);
       if (used_tile) *used_tile = 1;
       return (int)cudaGetLastError();
     }

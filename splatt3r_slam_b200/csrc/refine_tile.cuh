@@ -137,7 +137,7 @@ template <int FDIM, int RADIUS>
 __global__ void __launch_bounds__(THREADS, RT_BOX_KB > 113 ? 1 : 2)
 refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D21,
                    const int64_t *__restrict__ p1, int64_t *__restrict__ p1_new, int h, int w, int n,
-                   int qw, int dilation_max, int lin_out) {
+                   int qw, int bands, int dilation_max, int lin_out) {
   extern __shared__ __align__(128) unsigned char box_mem[];
   __shared__ uint64_t bar;
   __shared__ int red[2][THREADS / 32][8];
@@ -147,9 +147,14 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int tiles_x = (qw + TW - 1) / TW;
   const int qx = (blockIdx.x % tiles_x) * TW + (tid % TW);
-  const int qy = (blockIdx.x / tiles_x) * TH + (tid / TW);
+  // query rows are cut into `bands` bands of <= TH rows (band k = rows [k*qh/bands, (k+1)*qh/bands)): the host
+  // picks the band count whose tile count fills whole waves of SMs (512x384: 26 bands of 14-15 rows = 416
+  // tiles in 3 waves of 148, instead of 24 bands of 16 rows = 384 tiles in the same 3 waves)
+  const int band = blockIdx.x / tiles_x, qh = n / qw;
+  const int qy0 = (int)((long long)band * qh / bands), qy1 = (int)((long long)(band + 1) * qh / bands);
+  const int qy = qy0 + (tid / TW);
   const long long qlin = (long long)qy * qw + qx;
-  const bool active = qx < qw && qlin < n;
+  const bool active = qx < qw && qy < qy1;
   const size_t bq = (size_t)blockIdx.y * n + (active ? qlin : 0);
   const __half *img = D11 + (size_t)blockIdx.y * h * w * FDIM;
 
