@@ -40,6 +40,9 @@ namespace rtile {
 #ifndef RT_ISSUE_LANES
 #define RT_ISSUE_LANES 32
 #endif
+#ifndef RT_PAIRS
+#define RT_PAIRS 1  // two candidates per HMUL2/HADD2 (register transpose), see mac_chunk_pairs
+#endif
 #ifndef RT_PERMUTE_FIRST
 #define RT_PERMUTE_FIRST 0  // re-deal at the first (coarsest) level too
 #endif
@@ -97,6 +100,28 @@ __device__ __forceinline__ void mac_chunk(__half (&s)[NJ], const __half2 (&q4)[4
   }
 }
 
+// The same sums for candidate PAIRS: candidates 2p and 2p+1 of the column run in the two lanes of one HMUL2 +
+// HADD2 (their channel words are transposed in registers, 2 PRMT per word pair; the query channel is
+// broadcast by the operand selector).  Per 4 MACs: 2 PRMT + 2 HMUL2 + 2 HADD2 instead of 2 HMUL2 + 4 HADD +
+// the half extractions of the scalar form.  `_rn` intrinsics: a plain __hadd2(s, __hmul2(a, b)) would be
+// contracted into a single-rounding HFMA2.  The last odd candidate is paired with itself.
+template <int NJ>
+__device__ __forceinline__ void mac_chunk_pairs(__half2 (&s2)[(NJ + 1) / 2], const __half2 (&q4)[4], const uint4 (&c)[NJ]) {
+#pragma unroll
+  for (int t = 0; t < 4; t++) {
+    const __half2 qlo = __low2half2(q4[t]), qhi = __high2half2(q4[t]);
+#pragma unroll
+    for (int p = 0; p < (NJ + 1) / 2; p++) {
+      const int ja = 2 * p, jb = 2 * p + 1 < NJ ? 2 * p + 1 : 2 * p;
+      const uint32_t wa = t == 0 ? c[ja].x : t == 1 ? c[ja].y : t == 2 ? c[ja].z : c[ja].w;
+      const uint32_t wb = t == 0 ? c[jb].x : t == 1 ? c[jb].y : t == 2 ? c[jb].z : c[jb].w;
+      const __half2 a = *reinterpret_cast<const __half2 *>(&wa), bb = *reinterpret_cast<const __half2 *>(&wb);
+      s2[p] = __hadd2_rn(s2[p], __hmul2_rn(qlo, __lows2half2(a, bb)));
+      s2[p] = __hadd2_rn(s2[p], __hmul2_rn(qhi, __highs2half2(a, bb)));
+    }
+  }
+}
+
 struct Box {
   int x0, y0, bw, bh;  // origin and extent in pixels (bw*bh == 0: nothing staged)
 };
@@ -114,14 +139,27 @@ __device__ __forceinline__ void scan_column(const __half2 (&q)[FDIM / 2], int u,
     s[j] = __ushort_as_half(0);
     vv[j] = v0 + (j - RADIUS) * d;
   }
+#if RT_PAIRS
+  __half2 s2[(NJ + 1) / 2];
+#pragma unroll
+  for (int p = 0; p < (NJ + 1) / 2; p++) s2[p] = __half2half2(__ushort_as_half(0));
+#endif
 #pragma unroll
   for (int ch = 0; ch < FDIM / 8; ch++) {
     uint4 c[NJ];
 #pragma unroll
     for (int j = 0; j < NJ; j++) c[j] = load(min(max(vv[j], 0), h - 1), ch);
     const __half2 q4[4] = {q[ch * 4 + 0], q[ch * 4 + 1], q[ch * 4 + 2], q[ch * 4 + 3]};
+#if RT_PAIRS
+    mac_chunk_pairs<NJ>(s2, q4, c);
+#else
     mac_chunk<NJ>(s, q4, c);
+#endif
   }
+#if RT_PAIRS
+#pragma unroll
+  for (int j = 0; j < NJ; j++) s[j] = (j & 1) ? __high2half(s2[j / 2]) : __low2half(s2[j / 2]);
+#endif
 #pragma unroll
   for (int j = 0; j < NJ; j++) {  // reference scan order: j (v) inner, strict >
     const float sf = __half2float(s[j]);
