@@ -231,8 +231,9 @@ def _kernel_times(be, cfg, sets, steps):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this workload
-# (profiles/r01c_ncu_full_summary.txt; one 512x384 pair / N=2 E=2 graph): bytes
-NCU_TRAFFIC = {"iter_proj": 11.005e6, "refine": 22.116e6, "gn": 11.490e6}
+# (profiles/r01c_ncu_full_summary.txt, refine: profiles/r01g_ncu_refine_summary.txt; one 512x384 pair / N=2 E=2
+# graph): bytes
+NCU_TRAFFIC = {"iter_proj": 11.005e6, "refine": 23.135e6, "gn": 11.490e6}
 
 
 def run_graph(args):
