@@ -43,6 +43,9 @@ namespace rtile {
 #ifndef RT_PAIRS
 #define RT_PAIRS 1  // two candidates per HMUL2/HADD2 (register transpose), see mac_chunk_pairs
 #endif
+#ifndef RT_DEAL
+#define RT_DEAL 1  // how the re-deal places the queries that do not fit the one-per-class pattern (see the kernel)
+#endif
 #ifndef RT_PERMUTE_FIRST
 #define RT_PERMUTE_FIRST 0  // re-deal at the first (coarsest) level too
 #endif
@@ -300,10 +303,12 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
     // for ALL candidates of the level iff their pix0 differ mod 8.  The first level's centres are
     // adjacent pixels (conflict-free as dealt); afterwards they scatter (2.3 wavefronts per phase
     // measured), so the warp re-deals its 32 queries: the k-th query of residue class r goes to lane
-    // 8k + r, the rest (5th+ of a class, dead queries) fill the empty slots from the top quarter down.
+    // 8k + r, the rest (5th+ of a class, dead queries) fill the empty slots from the top quarter down
+    // (RT_DEAL=0) or are spread by class over the quarters that are not one-per-class (RT_DEAL=1, default).
     if ((RT_PERMUTE_FIRST || d < dilation_max) && !(split && pass)) {
       const unsigned lt = (1u << lane) - 1u;
       const int cls = live ? (((v0 - b.y0) * b.bw + (u0 - b.x0)) & 7) : 8;
+#if RT_DEAL == 0
       int n_slot = 0, rank = 0;
 #pragma unroll
       for (int r = 0; r < 8; r++) {
@@ -315,6 +320,27 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
       const bool spare = cls == 8 || rank >= 4;
       const unsigned spares = __ballot_sync(0xffffffffu, spare);
       const int dest = spare ? (int)__fns(empty, 31, -(__popc(spares & lt) + 1)) : (rank << 3 | cls);
+#else
+      // m = min(3, smallest class) quarters take exactly one query of every class (conflict-free); the other
+      // queries, ordered by class (dead ones last), are dealt round-robin to the remaining 4 - m quarters, so
+      // that a class with c members left puts at most ceil(c / (4 - m)) of them into one quarter
+      // (simulation, uniform residues: 1.82 wavefronts per phase against 2.00 for RT_DEAL=0 and 2.60 undealt).
+      int rank = 0, before = 0, nmin = 3;
+#pragma unroll
+      for (int r = 0; r < 9; r++) {
+        const unsigned m = __ballot_sync(0xffffffffu, cls == r);
+        const int nr = __popc(m);
+        if (cls == r) rank = __popc(m & lt);
+        if (cls > r) before += nr;  // queries of lower classes
+        if (r < 8) nmin = min(nmin, nr);
+      }
+      int dest;
+      if (cls < 8 && rank < nmin) dest = rank << 3 | cls;
+      else {
+        const int pos = before - nmin * min(cls, 8) + rank - (cls < 8 ? nmin : 0), nq = 4 - nmin;
+        dest = ((nmin + pos % nq) << 3) + pos / nq;
+      }
+#endif
       lane_of_slot[warp][dest] = (unsigned char)lane;
       __syncwarp();
       const int src = lane_of_slot[warp][lane];
