@@ -57,29 +57,50 @@ gn_persistent_kernel(float *Twc, const float *__restrict__ Xs, const float *__re
     const int64_t *idx_e = (second ? C.idx2 : idx) + (size_t)e * n;
     const uint8_t *val_e = (second ? C.valid2 : valid) + (size_t)e * n;
     const float *Q_e = (second ? C.Q2 : Q) + (size_t)e * n;
-    for (int g = g_begin + tid; g < g_end; g += PERSIST_THREADS) {
-      const uint32_t vm4 = __ldg(reinterpret_cast<const uint32_t *>(val_e) + g);
-      const longlong2 ia = __ldg(reinterpret_cast<const longlong2 *>(idx_e) + 2 * g);
-      const longlong2 ib = __ldg(reinterpret_cast<const longlong2 *>(idx_e) + 2 * g + 1);
-      const float4 q4 = __ldg(reinterpret_cast<const float4 *>(Q_e) + g);
-      const float4 c4 = __ldg(reinterpret_cast<const float4 *>(Cj_base) + g);
-      const float4 xa = __ldg(reinterpret_cast<const float4 *>(Xj_base) + 3 * g);
-      const float4 xb = __ldg(reinterpret_cast<const float4 *>(Xj_base) + 3 * g + 1);
-      const float4 xc = __ldg(reinterpret_cast<const float4 *>(Xj_base) + 3 * g + 2);
-      const long long ind[4] = {ia.x, ia.y, ib.x, ib.y};
-      const float qq[4] = {q4.x, q4.y, q4.z, q4.w};
-      const float cj[4] = {c4.x, c4.y, c4.z, c4.w};
-      float Xi[4][3], qs[4];
-      int iw[4];
+    // A CTA holds at most PERSIST_MAX_POINTS / 4 = 1408 groups = 2.75 per thread: all (<= 3) groups of a thread
+    // are loaded in ONE round of independent streaming loads (24 in flight per thread) followed by one round
+    // of gathers, instead of a load -> gather -> store chain per group (6 dependent HBM/L2 round trips).
+    constexpr int KMAX = (PERSIST_MAX_POINTS / 4 + PERSIST_THREADS - 1) / PERSIST_THREADS;
+    uint32_t vm4[KMAX];
+    longlong2 ia[KMAX], ib[KMAX];
+    float4 q4[KMAX], c4[KMAX], xa[KMAX], xb[KMAX], xc[KMAX];
+#pragma unroll
+    for (int k = 0; k < KMAX; k++) {
+      const int g = g_begin + tid + k * PERSIST_THREADS;
+      if (g < g_end) {
+        vm4[k] = __ldg(reinterpret_cast<const uint32_t *>(val_e) + g);
+        ia[k] = __ldg(reinterpret_cast<const longlong2 *>(idx_e) + 2 * g);
+        ib[k] = __ldg(reinterpret_cast<const longlong2 *>(idx_e) + 2 * g + 1);
+        q4[k] = __ldg(reinterpret_cast<const float4 *>(Q_e) + g);
+        c4[k] = __ldg(reinterpret_cast<const float4 *>(Cj_base) + g);
+        xa[k] = __ldg(reinterpret_cast<const float4 *>(Xj_base) + 3 * g);
+        xb[k] = __ldg(reinterpret_cast<const float4 *>(Xj_base) + 3 * g + 1);
+        xc[k] = __ldg(reinterpret_cast<const float4 *>(Xj_base) + 3 * g + 2);
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < KMAX; k++) {
+      const int g = g_begin + tid + k * PERSIST_THREADS;
+      if (g >= g_end) continue;
+      const long long ind[4] = {ia[k].x, ia[k].y, ib[k].x, ib[k].y};
+      const float qq[4] = {q4[k].x, q4[k].y, q4[k].z, q4[k].w};
+      const float cj[4] = {c4[k].x, c4[k].y, c4[k].z, c4[k].w};
+      float Xi[4][3], ci[4];
 #pragma unroll
       for (int t = 0; t < 4; t++) {
-        const bool vm = (vm4 >> (8 * t)) & 0xffu;
+        const bool vm = (vm4[k] >> (8 * t)) & 0xffu;
         const long long id = vm ? ind[t] : 0;  // gn_kernels.cu:912-913
         Xi[t][0] = __ldg(Xi_base + 3 * id);
         Xi[t][1] = __ldg(Xi_base + 3 * id + 1);
         Xi[t][2] = __ldg(Xi_base + 3 * id + 2);
-        const float ci = __ldg(Ci_base + id);
-        const bool ok = vm && (qq[t] > C.Q_thresh) && (ci > C.C_thresh) && (cj[t] > C.C_thresh);
+        ci[t] = __ldg(Ci_base + id);
+      }
+      float qs[4];
+      int iw[4];
+#pragma unroll
+      for (int t = 0; t < 4; t++) {
+        const bool vm = (vm4[k] >> (8 * t)) & 0xffu;
+        const bool ok = vm && (qq[t] > C.Q_thresh) && (ci[t] > C.C_thresh) && (cj[t] > C.C_thresh);
         qs[t] = ok ? qq[t] : -INFINITY;  // fails "q > Q_thresh" in point_contrib => point skipped
         iw[t] = (int)ind[t];
       }
@@ -89,9 +110,9 @@ gn_persistent_kernel(float *Twc, const float *__restrict__ Xs, const float *__re
       a[0 * st4] = make_float4(Xi[0][0], Xi[1][0], Xi[2][0], Xi[3][0]);
       a[1 * st4] = make_float4(Xi[0][1], Xi[1][1], Xi[2][1], Xi[3][1]);
       a[2 * st4] = make_float4(Xi[0][2], Xi[1][2], Xi[2][2], Xi[3][2]);
-      a[3 * st4] = make_float4(xa.x, xa.w, xb.z, xc.y);
-      a[4 * st4] = make_float4(xa.y, xb.x, xb.w, xc.z);
-      a[5 * st4] = make_float4(xa.z, xb.y, xc.x, xc.w);
+      a[3 * st4] = make_float4(xa[k].x, xa[k].w, xb[k].z, xc[k].y);
+      a[4 * st4] = make_float4(xa[k].y, xb[k].x, xb[k].w, xc[k].z);
+      a[5 * st4] = make_float4(xa[k].z, xb[k].y, xc[k].x, xc[k].w);
       a[6 * st4] = make_float4(qs[0], qs[1], qs[2], qs[3]);
       a[7 * st4] = make_float4(__int_as_float(iw[0]), __int_as_float(iw[1]), __int_as_float(iw[2]),
                                __int_as_float(iw[3]));

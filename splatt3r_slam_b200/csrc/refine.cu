@@ -14,9 +14,13 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <stdlib.h>
 #include "../../include/b200slam.h"
 #include "refine_tile.cuh"
 
+#ifndef RT_BAND_FIXED
+#define RT_BAND_FIXED 6
+#endif
 namespace {
 
 constexpr int RF_THREADS = 128;
@@ -191,9 +195,13 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
 #ifndef RT_NO_BANDS
     long long best = -1;
     for (int nb = bands_min; nb <= bands_min + bands_min / 2 && nb <= h; nb++) {
-      const long long waves = ((long long)tiles_x * nb * b + n_sm - 1) / n_sm, rows = (h + nb - 1) / nb;
+      // time of a tile ~ its query rows + a fixed part (box staging, barriers, halo) worth RT_BAND_FIXED rows
+      const long long waves = ((long long)tiles_x * nb * b + n_sm - 1) / n_sm, rows = (h + nb - 1) / nb + RT_BAND_FIXED;
       if (best < 0 || waves * rows < best) { best = waves * rows; bands = nb; }
     }
+    static int forced = -1;  // tuning aid: B200SLAM_REFINE_BANDS=<n> overrides the choice
+    if (forced < 0) { const char *e = getenv("B200SLAM_REFINE_BANDS"); forced = e ? atoi(e) : 0; }
+    if (forced >= bands_min && forced <= h) bands = forced;
 #endif
     const int tiles = tiles_x * bands;
     // a level whose full nominal box does not fit is scanned in two column passes of half the reach in x
