@@ -197,7 +197,7 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
     for (int nb = bands_min; nb <= bands_min + bands_min / 2 && nb <= h; nb++) {
       // time of a tile ~ its query rows + a fixed part (box staging, barriers, halo) worth RT_BAND_FIXED rows
       const long long waves = ((long long)tiles_x * nb * b + n_sm - 1) / n_sm, rows = (h + nb - 1) / nb + RT_BAND_FIXED;
-      if (best < 0 || waves * rows < best) { best = waves * rows; bands = nb; }
+      if (best < 0 || waves * rows <= best) { best = waves * rows; bands = nb; }  // ties: more, smaller tiles
     }
     static int forced = -1;  // tuning aid: B200SLAM_REFINE_BANDS=<n> overrides the choice
     if (forced < 0) { const char *e = getenv("B200SLAM_REFINE_BANDS"); forced = e ? atoi(e) : 0; }
