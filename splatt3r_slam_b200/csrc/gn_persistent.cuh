@@ -125,10 +125,9 @@ gn_persistent_kernel(float *Twc, const float *__restrict__ Xs, const float *__re
   const int lane = tid & 31, warp = tid >> 5;
   __shared__ float red[PERSIST_THREADS / 32][NACC];
   __shared__ bool is_last;
+  if (tid < 16) pose_sm[tid] = __ldcg(Twc + 8 * (tid < 8 ? ix : jx) + (tid & 7));
+  __syncthreads();
   for (int it = 0; it < max_iter; it++) {
-    // current poses of the edge's two keyframes, straight from L2 (another SM's tail wrote them)
-    if (tid < 16) pose_sm[tid] = __ldcg(Twc + 8 * (tid < 8 ? ix : jx) + (tid & 7));
-    __syncthreads();
     const EdgePose P = rel_pose(pose_sm, pose_sm + 8);
 
     float acc[NACC];
@@ -168,14 +167,17 @@ gn_persistent_kernel(float *Twc, const float *__restrict__ Xs, const float *__re
       small_tail<PERSIST_THREADS>(Twc, ii_row, jj_row, partials, S, E, N, delta_thresh, dx, edge_blocks, state);
       __syncthreads();
       if (tid == 0) {
-        flag_sm = state->done;
         __threadfence();
         st_release_u32(&state->gen, (unsigned)(it + 1));  // opens the grid barrier
       }
     } else if (tid == 0) {
       while (ld_acquire_u32(&state->gen) < (unsigned)(it + 1)) __nanosleep(20);
-      flag_sm = __ldcg(&state->done);
     }
+    __syncthreads();
+    // one L2 round trip for everything the next iteration needs: the two poses of this CTA's edge (the tail
+    // on another SM wrote them) and the convergence flag
+    if (tid < 16) pose_sm[tid] = __ldcg(Twc + 8 * (tid < 8 ? ix : jx) + (tid & 7));
+    if (tid == 16) flag_sm = __ldcg(&state->done);
     __syncthreads();
     if (flag_sm) break;  // ||dx|| < delta: same early exit on every CTA
   }

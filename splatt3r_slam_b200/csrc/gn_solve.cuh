@@ -431,15 +431,15 @@ __device__ inline void finalize_small(const float *Twc, const int64_t *ii_row, c
     const int item = t % items, chunk = t / items, e = item / NACC, l = item - e * NACC;
     const double *p = partials + (size_t)e * S * NACC + l;
     double sum = 0.0;
-    for (int k0 = chunk; k0 < S; k0 += 8 * NC) {  // 8 independent loads in flight per round trip
-      double v[8];
+    for (int k0 = chunk; k0 < S; k0 += 12 * NC) {  // 12 independent loads in flight per round trip (tracker: S = 74, NC = 7: one trip)
+      double v[12];
 #pragma unroll
-      for (int u = 0; u < 8; u++) {
+      for (int u = 0; u < 12; u++) {
         const int k = k0 + u * NC;
         v[u] = k < S ? __ldcg(p + (size_t)k * NACC) : 0.0;
       }
 #pragma unroll
-      for (int u = 0; u < 8; u++) sum += v[u];
+      for (int u = 0; u < 12; u++) sum += v[u];
     }
     tmp[t] = sum;
   }
