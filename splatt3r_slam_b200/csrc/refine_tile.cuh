@@ -189,7 +189,7 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
   const int tiles_x = (qw + TW - 1) / TW;
   const int qx = (blockIdx.x % tiles_x) * TW + (tid % TW);
   // query rows are cut into `bands` bands of <= TH rows (band k = rows [k*qh/bands, (k+1)*qh/bands)): the host
-  // picks the band count whose tile count fills whole waves of SMs (512x384: 26 bands of 14-15 rows = 416
+  // picks the band count whose tile count fills whole waves of SMs (512x384: 27 bands of 14-15 rows = 432
   // tiles in 3 waves of 148, instead of 24 bands of 16 rows = 384 tiles in the same 3 waves)
   const int band = blockIdx.x / tiles_x, qh = n / qw;
   const int qy0 = (int)((long long)band * qh / bands), qy1 = (int)((long long)(band + 1) * qh / bands);
