@@ -16,6 +16,9 @@
 namespace b200gn {
 
 // ---- workspace layout -------------------------------------------------------------------------
+#ifndef B200SLAM_SINGLE_CTA_MAX_D
+#define B200SLAM_SINGLE_CTA_MAX_D 217  // largest system of the single-CTA packed solver (A/B: lower it to route mid-size graphs to the tiled solver)
+#endif
 struct State {  // head of the workspace
   int iters;      // iterations executed so far
   int done;       // set when ||dx|| < delta_thresh: later launches are no-ops
@@ -87,9 +90,9 @@ inline Layout make_layout(int N, int E, int n) {
   L.A = off;
   off = align256(off + D * D * sizeof(double));
   L.dense_ctrl = off;
-  if (D > 217) off = align256(off + 256 + ((D + 63) / 64) * 64 * 64 * sizeof(double));
+  if (D > B200SLAM_SINGLE_CTA_MAX_D) off = align256(off + 256 + ((D + 63) / 64) * 64 * 64 * sizeof(double));
   L.pcg = off;
-  if (D > 217)
+  if (D > B200SLAM_SINGLE_CTA_MAX_D)
     off = align256(off + 256 + align256((2 * (D / 7) + 2 + 2 * (size_t)E) * sizeof(int)) +
                    (49 * (D / 7) + 4 * D + 4 * 148) * sizeof(double));
   L.rhs = off; off = align256(off + D * sizeof(double));

@@ -340,7 +340,7 @@ __device__ inline void finish_update(bool ok, const double *x, double *scratch, 
 namespace b200gn {
 
 constexpr int SOLVE_THREADS = 512;
-constexpr int PACKED_MAX_D = 217;  // 217*218/2*8 = 189 KB of packed lower triangle in smem
+constexpr int PACKED_MAX_D = B200SLAM_SINGLE_CTA_MAX_D;  // 217*218/2*8 = 189 KB of packed lower triangle in smem
 
 // dynamic smem: [x: Dp][col: Dp][packed L: D(D+1)/2][Pt: CB*ldp][Dg: CB*CB + CB] if PACKED, else [x][col]
 __host__ __device__ inline int chol_ldp(int D) { return ((D + 3) & ~3) + 4; }

@@ -135,11 +135,14 @@ def test_error_convention(backend):
                                torch.zeros(1, 64, 2, device=dev(), dtype=torch.int64), 3, 5)
 
 
-def test_refine_tiled_kernel_incoherent_and_out_of_range(backend):
-    """n == h*w selects the tiled (bulk-copy staged) kernel.  Random centres make every tile
-    incoherent (global-memory path per query), a coherent half exercises the staged path, and
-    centres far outside the image / beyond int32 must be returned untouched."""
-    h, w, fdim = 40, 56, 24
+@pytest.mark.parametrize("h,w", [(40, 56), (45, 72), (50, 96)])
+def test_refine_tiled_kernel_incoherent_and_out_of_range(backend, h, w):
+    """n == h*w selects the tiled (bulk-copy staged) kernel when w >= 32 + 6*dilation_max + 2 (w = 56: dilation
+    1 and 3 only; 72 and 96: all three, with a ragged last tile column and row bands of unequal height).
+    Random centres make every tile incoherent (global-memory path per query, lanes re-dealt at every
+    level), a coherent half exercises the staged path, and centres far outside the image / beyond int32
+    must be returned untouched."""
+    fdim = 24
     n = h * w
     g = torch.Generator().manual_seed(5)
     D11 = torch.nn.functional.normalize(torch.randn(2, h, w, fdim, generator=g), dim=-1).half()
