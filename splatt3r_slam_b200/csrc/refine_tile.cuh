@@ -46,6 +46,9 @@ namespace rtile {
 #ifndef RT_DEAL
 #define RT_DEAL 1  // how the re-deal places the queries that do not fit the one-per-class pattern (see the kernel)
 #endif
+#ifndef RT_MERGE
+#define RT_MERGE 1  // stage one box for all remaining levels as soon as it fits
+#endif
 #ifndef RT_PERMUTE_FIRST
 #define RT_PERMUTE_FIRST 0  // re-deal at the first (coarsest) level too
 #endif
@@ -236,6 +239,8 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
 #endif
   __syncthreads();  // mbarrier initialised
 
+  Box b{0, 0, 0, 0};
+  bool merged = false;  // b already holds every pixel the remaining levels can touch: no more barriers or copies
   for (int pass = 0, d = dilation_max; d > 0; pass++) {
     const int rd = RADIUS * d;
     // A level whose nominal box (tile + reach + SLACK px) exceeds the shared-memory box is
@@ -243,6 +248,8 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
     // with a box of half the reach in x.  With the default 224 KB box no level splits.
     const bool split = (TW + 2 * rd + SLACK) * (TH + 2 * rd + SLACK) > MAX_PX;
     const int ilo = split && pass ? d : -rd, ihi = split && !pass ? 0 : rd;
+    bool fresh = false;  // a copy was issued in this pass
+    if (!merged) {
     // ---- bounding box of the centres of this tile (queries that can hit the image only) --------
     // One block barrier per pass: every warp leaves its partial box in shared memory, and after the
     // barrier EVERY warp reduces the partials itself (shuffles), so nobody waits for an elected thread;
@@ -269,10 +276,21 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
 #pragma unroll
       for (int k = 4; k < 7; k++) vals[k] = __reduce_add_sync(0xffffffffu, has ? redp[lane][k] : 0);
     }
-    Box b{0, 0, 0, 0};
+    b = Box{0, 0, 0, 0};
     {
       const int umin = vals[0], numax = vals[1], vmin = vals[2], nvmax = vals[3], su = vals[4], sv = vals[5], c = vals[6];
-      if (c > 0) {
+      if (c > 0 && RT_MERGE && !split) {
+        // One box for ALL remaining levels (total reach RADIUS * (d + ... + 1)) if it fits: the finer levels
+        // then run without block barriers, box reductions or copies (warps drift apart freely).
+        const int rall = RADIUS * d * (d + 1) / 2;
+        const int x0 = max(umin - rall, 0), x1 = min(-numax + rall, w - 1);
+        const int y0 = max(vmin - rall, 0), y1 = min(-nvmax + rall, h - 1);
+        if (x1 >= x0 && y1 >= y0 && (x1 - x0 + 1) * (y1 - y0 + 1) <= MAX_PX) {
+          b = Box{x0, y0, x1 - x0 + 1, y1 - y0 + 1};
+          merged = true;
+        }
+      }
+      if (c > 0 && !merged) {
         int x0 = max(umin + ilo, 0), x1 = min(-numax + ihi, w - 1);
         int y0 = max(vmin - rd, 0), y1 = min(-nvmax + rd, h - 1);
         if (x1 >= x0 && y1 >= y0) {
@@ -295,6 +313,8 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
       if (lane < RT_ISSUE_LANES)
         for (int r = lane; r < b.bh; r += RT_ISSUE_LANES)
           bulk_g2s(box_mem + (size_t)r * row_bytes, img + ((size_t)(b.y0 + r) * w + b.x0) * FDIM, row_bytes, &bar);
+    }
+    fresh = b.bw * b.bh > 0;
     }
     const bool staged = b.bw * b.bh > 0;
 #if RT_PERMUTE
@@ -359,7 +379,7 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
       v_new = v0;
     }
 #endif
-    if (staged) {  // (the re-deal above needs only the box geometry: it overlaps the copy)
+    if (fresh) {  // (the re-deal above needs only the box geometry: it overlaps the copy)
       mbar_wait(&bar, parity);
       parity ^= 1u;
     }
