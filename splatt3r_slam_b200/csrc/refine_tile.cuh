@@ -50,7 +50,7 @@ namespace rtile {
 #define RT_MERGE 1  // stage one box for all remaining levels as soon as it fits
 #endif
 #ifndef RT_PERMUTE_FIRST
-#define RT_PERMUTE_FIRST 0  // re-deal at the first (coarsest) level too
+#define RT_PERMUTE_FIRST 1  // re-deal at the first (coarsest) level too (191.9 vs 193.4 us with the class-balanced deal)
 #endif
 #ifndef RT_PERMUTE
 #define RT_PERMUTE 1  // re-deal the queries of a warp to its lanes per level so that quarter-warps hit distinct banks
@@ -321,8 +321,8 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
     // Candidate (i, j) of a query sits at box pixel pix0 + j*bw + i, and a 16-byte chunk of pixel p lies in
     // bank group (3p + chunk) mod 8: the 8 lanes of a quarter-warp (one LDS.128 phase) are conflict-free
     // for ALL candidates of the level iff their pix0 differ mod 8.  The first level's centres are
-    // adjacent pixels (conflict-free as dealt); afterwards they scatter (2.3 wavefronts per phase
-    // measured), so the warp re-deals its 32 queries: the k-th query of residue class r goes to lane
+    // nearly adjacent pixels (truncation skips / repeats some); afterwards they scatter (2.3 wavefronts per
+    // phase measured), so the warp re-deals its 32 queries: the k-th query of residue class r goes to lane
     // 8k + r, the rest (5th+ of a class, dead queries) fill the empty slots from the top quarter down
     // (RT_DEAL=0) or are spread by class over the quarters that are not one-per-class (RT_DEAL=1, default).
     if ((RT_PERMUTE_FIRST || d < dilation_max) && !(split && pass)) {
