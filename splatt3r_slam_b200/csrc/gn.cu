@@ -9,8 +9,10 @@
 #include <math.h>
 #include <stdint.h>
 #include <stdlib.h>
+#include <string.h>
 
 #include "../../include/b200slam.h"
+#include "dev_cache.cuh"
 #include "gn_build.cuh"
 
 namespace b200gn {
@@ -136,7 +138,7 @@ build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__
 #pragma unroll
   for (int l = 0; l < NACC; l++) acc[l] = 0.0f;
 
-  const bool vec_ok = (n & 3) == 0;          // 16-byte loads need every edge row 16-byte aligned
+  const bool vec_ok = C.vec_ok != 0;         // 16-byte loads: n % 4 == 0 and aligned bases (set_alignment)
   const int groups = vec_ok ? (n >> 2) : 0;  // groups of 4 points
   const int gper = (groups + S - 1) / S;
   const int g_begin = s * gper, g_end = min(groups, g_begin + gper);

@@ -20,6 +20,14 @@ inline BuildConsts make_consts(const b200slam_gn_params *p, const float *K) {
   return C;
 }
 
+// BuildConsts::vec_ok: the vectorised (4 points per 16-byte load) paths need n % 4 == 0 and aligned bases.
+inline void set_alignment(BuildConsts &C, const void *Xs, const void *Cs, const void *idx, const void *valid,
+                          const void *Q, int n) {
+  auto al = [](const void *p, uintptr_t a) { return p == nullptr || ((uintptr_t)p % a) == 0; };
+  C.vec_ok = (n & 3) == 0 && al(Xs, 16) && al(Cs, 16) && al(idx, 16) && al(Q, 16) && al(valid, 4) &&
+             al(C.idx2, 16) && al(C.Q2, 16) && al(C.valid2, 4);
+}
+
 inline int check_K(const b200slam_gn_params *p, const float *K) {
   return (p->kind == B200SLAM_GN_CALIB && !K) ? B200SLAM_EINVAL : 0;
 }
@@ -119,12 +127,7 @@ inline int launch_pcg(float *Twc, const int64_t *ii_row, const int64_t *jj_row, 
   adj_fill_kernel<<<nb, tb, 0, st>>>(ii_row, jj_row, E, M, B.adj_ptr, B.adj_list);
   rc = (int)cudaGetLastError();
   if (rc) return rc;
-  static int num_sms = 0;
-  if (num_sms == 0) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-  }
+  const int num_sms = b200dev::info().num_sms;
   int grid = (M + PCG_WARPS - 1) / PCG_WARPS;
   if (grid > num_sms) grid = num_sms;
   if (grid > PCG_MAX_CTAS) grid = PCG_MAX_CTAS;
@@ -154,12 +157,12 @@ inline int launch_dense(float *Twc, const int64_t *ii_row, const int64_t *jj_row
   assemble_kernel<<<M, 256, 0, st>>>(ii_row, jj_row, edge_blocks, E, D, B.A, B.b, state);
   rc = (int)cudaGetLastError();
   if (rc) return rc;
-  static int grid_ctas = 0;  // all co-resident: SMs x resident CTAs per SM (2 with 68 KB of shared memory each)
+  static b200dev::PerDeviceInt grid_cache;  // all co-resident: SMs x resident CTAs per SM (2 with 68 KB of shared memory each)
+  int &grid_ctas = grid_cache.ref();
   const size_t smem = (size_t)DENSE_SMEM_DOUBLES * sizeof(double);
   if (grid_ctas == 0) {
-    int dev = 0, num_sms = 0, per_sm = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
+    int per_sm = 0;
+    const int num_sms = b200dev::info().num_sms;
     cudaFuncSetAttribute(dense_solve_retract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, dense_solve_retract_kernel, DENSE_THREADS, smem);
     static const char *env = getenv("B200SLAM_GN_DENSE_CTAS_PER_SM");  // tuning aid
@@ -188,11 +191,9 @@ inline int launch_solve(float *Twc, const int64_t *ii_row, const int64_t *jj_row
   int rc = (int)cudaGetLastError();
   if (rc) return rc;
   const size_t smem = solve_smem_bytes(D, Dp, true);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static b200dev::Once attr;
+  if (attr.first())
     cudaFuncSetAttribute(solve_retract_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-    attr_set = true;
-  }
   solve_retract_kernel<true><<<1, SOLVE_THREADS, smem, st>>>(Twc, A, rhs, N, D, Dp, delta_thresh, dx, state);
   return (int)cudaGetLastError();
 }
@@ -201,12 +202,11 @@ inline int launch_solve(float *Twc, const int64_t *ii_row, const int64_t *jj_row
 // (caller falls back to one launch per iteration), 0 on success, a CUDA error otherwise.
 template <int KIND>
 inline int launch_persistent_kind(dim3 grid, size_t smem, cudaStream_t st, void **args) {
-  static bool attr_set = false;
-  if (!attr_set) {
+  static b200dev::Once attr;
+  if (attr.first()) {
     cudaError_t err = cudaFuncSetAttribute(gn_persistent_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            PERSIST_WORDS * PERSIST_MAX_POINTS * (int)sizeof(float));
-    if (err != cudaSuccess) return (int)err;
-    attr_set = true;
+    if (err != cudaSuccess) { attr.retry(); return (int)err; }
   }
   return (int)cudaLaunchCooperativeKernel((const void *)gn_persistent_kernel<KIND>, grid, dim3(PERSIST_THREADS), args,
                                           smem, st);
@@ -217,15 +217,9 @@ inline int try_persistent(const b200slam_gn_params *p, BuildConsts C, float *Twc
                           const float *Q, int N, int E, int n, int max_iter, float delta_thresh, float *dx,
                           double *partials, double *edge_blocks, State *state, cudaStream_t st) {
   static const bool disabled = getenv("B200SLAM_GN_NO_PERSIST") != nullptr;  // tuning aid
-  static int num_sms = 0;
-  if (num_sms == 0) {
-    int dev = 0, coop = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-    if (!coop) num_sms = -1;
-  }
-  if (disabled || num_sms < 1 || E < 1 || E > num_sms || (n & 3) || max_iter < 1) return 1;
+  const b200dev::Info dev = b200dev::info();
+  const int num_sms = dev.coop ? dev.num_sms : -1;
+  if (disabled || num_sms < 1 || E < 1 || E > num_sms || !C.vec_ok || max_iter < 1) return 1;
   const int S = num_sms / E;  // one CTA per SM, all co-resident
   const int groups = n >> 2, gper = (groups + S - 1) / S;
   if (4 * gper > PERSIST_MAX_POINTS || (size_t)E * S > partial_slots(E)) return 1;
@@ -286,7 +280,8 @@ extern "C" int b200slam_gn_edge_blocks(const b200slam_gn_params *prm, const floa
   cudaStream_t st = (cudaStream_t)stream;
   int rc = check_K(prm, K);
   if (rc) return rc;
-  const BuildConsts C = make_consts(prm, K);
+  BuildConsts C = make_consts(prm, K);
+  set_alignment(C, Xs, Cs, idx, valid, Q, n);
   return launch_edge_blocks(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, E, n, e0, Ecount,
                             edge_blocks, (char *)workspace, L, st);
 }
@@ -374,8 +369,10 @@ extern "C" int b200slam_gauss_newton(const b200slam_gn_params *prm, float *Twc, 
   if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
   int rc = check_K(prm, K);
   if (rc) return rc;
-  return gauss_newton_run(prm, make_consts(prm, K), Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, N, E, n, max_iter,
-                          delta_thresh, dx, (char *)workspace, L, (cudaStream_t)stream);
+  BuildConsts C = make_consts(prm, K);
+  set_alignment(C, Xs, Cs, idx, valid, Q, n);
+  return gauss_newton_run(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, N, E, n, max_iter, delta_thresh, dx,
+                          (char *)workspace, L, (cudaStream_t)stream);
 }
 
 extern "C" int b200slam_gauss_newton_ids(const b200slam_gn_params *prm, float *Twc, const float *Xs,
@@ -429,6 +426,7 @@ extern "C" int b200slam_gauss_newton_twoway(const b200slam_gn_params *prm, float
   C.idx2 = idx_jj2ii - (size_t)E1 * n;  // so that (idx2 + e * n) addresses row e - E1
   C.valid2 = valid_match_i - (size_t)E1 * n;
   C.Q2 = Q_jj2ii - (size_t)E1 * n;
+  set_alignment(C, Xs, Cs, idx_ii2jj, valid_match_j, Q_ii2jj, n);
   return gauss_newton_run(prm, C, Twc, Xs, Cs, rows, rows + 2 * (size_t)E1, idx_ii2jj, valid_match_j, Q_ii2jj, N, E,
                           n, max_iter, delta_thresh, dx, ws, L, st);
 }

@@ -100,6 +100,9 @@ struct BuildConsts {
   const int64_t *idx2 = nullptr;
   const uint8_t *valid2 = nullptr;
   const float *Q2 = nullptr;
+  // 16-byte loads are legal: n % 4 == 0 AND every base pointer is 16-byte aligned (valid: 4-byte); a
+  // contiguous view with an odd storage offset takes the scalar path instead of faulting
+  int vec_ok = 0;
 };
 
 // One point.  Xi/ci = matched point of keyframe i, Xj/cj = point k of keyframe j.

@@ -537,7 +537,8 @@ __device__ inline void small_tail(float *Twc, const int64_t *ii_row, const int64
   __shared__ int fail;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int D = 7 * (N - NUM_FIX);
-  __shared__ double ebs[SMALL_FIN_E * 56], fin_tmp[NT];
+  // finalize_small writes items * NC <= max(NT, SMALL_FIN_E * NACC) doubles (E = 8: 280 items > 256 threads)
+  __shared__ double ebs[SMALL_FIN_E * 56], fin_tmp[NT > SMALL_FIN_E * NACC ? NT : SMALL_FIN_E * NACC];
   if (E <= SMALL_FIN_E) {  // few edges (the tracker): whole-CTA stage 2, blocks stay in shared memory
     finalize_small<NT>(Twc, ii_row, partials, S, E, ebs, sc, fin_tmp);
     edge_blocks = ebs;

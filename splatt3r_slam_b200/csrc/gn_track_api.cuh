@@ -15,26 +15,19 @@ int launch_track(const float *Xf, const float *B, const float *Qk, const uint8_t
   if (!T_WCf || !T_WCk || !T_WCf_new || !T_CkCf) return B200SLAM_EINVAL;
   if (n > 0 && (!Xf || !B || !Qk || !valid || (KIND == 1 && !valid2))) return B200SLAM_EINVAL;
   if (!workspace || workspace_bytes < b200slam_track_workspace_bytes()) return B200SLAM_EWORKSPACE;
-  static int num_sms = 0;
-  if (num_sms == 0) {
-    int dev = 0, coop = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&num_sms, cudaDevAttrMultiProcessorCount, dev);
-    cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
-    if (!coop) num_sms = -1;
-  }
-  if (num_sms < 1) return B200SLAM_EINVAL;
+  const b200dev::Info dev = b200dev::info();  // per device, not per process
+  if (!dev.coop) return B200SLAM_EINVAL;
+  const int num_sms = dev.num_sms;
   int S = num_sms > 1024 ? 1024 : num_sms;
   int gper = (n + S - 1) / S;
   gper = (gper + 31) / 32 * 32;
   if (gper < 32) gper = 32;
   if (gper > PERSIST_MAX_POINTS) return B200SLAM_EINVAL;  // > 833 k points on 148 SMs
-  static bool attr_set = false;
-  if (!attr_set) {
+  static b200dev::Once attr;
+  if (attr.first()) {
     cudaError_t err = cudaFuncSetAttribute(track_kernel<KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                            PERSIST_WORDS * PERSIST_MAX_POINTS * (int)sizeof(float));
-    if (err != cudaSuccess) return (int)err;
-    attr_set = true;
+    if (err != cudaSuccess) { attr.retry(); return (int)err; }
   }
   cudaStream_t st = (cudaStream_t)stream;
   TrackState *state = (TrackState *)workspace;

@@ -16,6 +16,7 @@
 
 #include <stdlib.h>
 #include "../../include/b200slam.h"
+#include "dev_cache.cuh"
 #include "refine_tile.cuh"
 
 #ifndef RT_BAND_FIXED
@@ -184,12 +185,7 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
   const int reach = radius * dilation_max;
   if (fdim == 24 && aligned && radius == 3 && n == h * w && dilation_max >= 1 && w >= rtile::TW + 2 * reach + 2) {
     // band count: fewest waves x rows-per-tile (time of a tile ~ its query rows); see refine_tile.cuh
-    static int n_sm = 0;
-    if (!n_sm) {
-      int dev = 0;
-      cudaGetDevice(&dev);
-      if (cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n_sm < 1) n_sm = 148;
-    }
+    const int n_sm = b200dev::info().num_sms;
     const int tiles_x = (w + rtile::TW - 1) / rtile::TW, bands_min = (h + rtile::TH - 1) / rtile::TH;
     int bands = bands_min;
 #ifndef RT_NO_BANDS
@@ -208,12 +204,10 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
     long long nominal = (long long)(rtile::TW + 2 * reach + rtile::SLACK) * (rtile::TH + 2 * reach + rtile::SLACK) * fdim * 2;
     if (nominal > rtile::BOX_BYTES) nominal = (long long)(rtile::TW + reach + 2) * (rtile::TH + 2 * reach + 2) * fdim * 2;
     if (nominal <= rtile::BOX_BYTES) {
-      static bool attr_set = false;
-      if (!attr_set) {
+      static b200dev::Once attr;  // function attributes are per device
+      if (attr.first())
         cudaFuncSetAttribute(rtile::refine_tile_kernel<24, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                              rtile::BOX_BYTES);
-        attr_set = true;
-      }
       rtile::refine_tile_kernel<24, 3><<<dim3(tiles, b), rtile::THREADS, rtile::BOX_BYTES, st>>>(
           a, q, p1, p1_new, h, w, n, w, bands, dilation_max, lin_out);
       if (used_tile) *used_tile = 1;
