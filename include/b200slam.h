@@ -148,6 +148,18 @@ int b200slam_gn_solve_retract(float *Twc, const int64_t *ii_row, const int64_t *
 int b200slam_gn_reset(void *workspace, size_t workspace_bytes, void *stream);
 /* Read back {iterations executed, done flag, cholesky failures} (synchronises the stream). */
 int b200slam_gn_status(const void *workspace, int *iters, int *done, int *chol_fail, void *stream);
+/* Large-graph (7(N-1) > 217) solver selection, process-wide: -1 = default (environment B200SLAM_GN_SOLVER,
+ * else auto), 0 = auto (pipelined PCG, exact tiled Cholesky as gated fallback), 1 = exact tiled Cholesky
+ * only, 2 = first-generation PCG.  A/B and test aid; all three solve the same system (the reference's
+ * SparseBlock::solve, gn_kernels.cu:131-152). */
+int b200slam_gn_set_solver(int mode);
+/* Large-graph solver diagnostics of the last call on this workspace (synchronises the stream): the
+ * reference's counterpart is SparseBlock::solve's solver.info() (gn_kernels.cu:141-149), which it does not
+ * expose.  cg_iters / cg_rel / cg_true_rel: iterations and relative (r, D^-1 r) — recursive and true — of
+ * the last pipelined-PCG solve; cg_total: PCG iterations summed over the call; pcg_bad: the PCG gave up and
+ * the exact tiled Cholesky took over; dense_runs: how many exact solves the call executed. */
+int b200slam_gn_solver_status(const void *workspace, int *cg_iters, int *cg_total, int *pcg_bad,
+                              int *dense_runs, double *cg_rel, double *cg_true_rel, void *stream);
 
 /* Whole driver: replaces gauss_newton_{rays,calib,points}_cuda (gn_kernels.cu:1139-1227,
  * :1545-1637, :724-810) for a single GPU.  Enqueues max_iter iterations with no host

@@ -30,6 +30,11 @@ struct State {  // head of the workspace
   unsigned gen;  // grid-barrier generation of the persistent kernel (= iterations completed)
   int cg_iters;        // PCG iterations of the last large-graph solve
   double cg_rel;       // its final r^T M^-1 r relative to the initial value
+  double cg_true_rel;  // pipelined PCG: the same quantity for the TRUE residual b - H x of the returned x
+  int pcg_bad;         // pipelined PCG gave up (not converged / not SPD): the exact Cholesky runs instead, for the rest of the call
+  int adj_ready;       // pose adjacency lists of the PCG solvers are built (once per call, the topology is fixed)
+  int cg_total;        // PCG iterations summed over the call
+  int dense_runs;      // number of exact tiled-Cholesky solves of the call
 };
 __device__ __forceinline__ unsigned long long gtimer() {
   unsigned long long t;
@@ -41,7 +46,7 @@ constexpr size_t STATE_BYTES = 256;
 __host__ __device__ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Layout {
-  size_t partials, edge_blocks, A, dense_ctrl, pcg, rhs, rows, first, total;
+  size_t partials, edge_blocks, A, dense_ctrl, pcg, pcg2, rhs, rows, first, total;
 };
 
 // Number of CTAs (S) that split the n points of one edge when `Ecount` edges are built by one
@@ -97,6 +102,11 @@ inline Layout make_layout(int N, int E, int n) {
   if (D > B200SLAM_SINGLE_CTA_MAX_D)
     off = align256(off + 256 + align256((2 * (D / 7) + 2 + 2 * (size_t)E) * sizeof(int)) +
                    (49 * (D / 7) + 4 * D + 4 * 148) * sizeof(double));
+  // pipelined PCG (gn_pcg2.cuh): [xch 2*D | partial sums 2*160*2 (doubles) | tags 2*160 (u32)]; shares the adjacency of L.pcg
+  L.pcg2 = off;
+  if (D > B200SLAM_SINGLE_CTA_MAX_D)
+    off = align256(off + align256(2 * D * sizeof(double)) + align256((size_t)2 * 160 * 2 * sizeof(double)) +
+                   align256((size_t)2 * 160 * sizeof(unsigned)));
   L.rhs = off; off = align256(off + D * sizeof(double));
   L.rows = off; off = align256(off + (size_t)2 * E * sizeof(int64_t));
   L.first = off; off = align256(off + (size_t)2 * E);
@@ -275,6 +285,7 @@ __global__ void export_blocks_kernel(const double *__restrict__ edge_blocks, int
 #include "gn_persistent.cuh"
 #include "gn_track.cuh"
 #include "gn_pcg.cuh"
+#include "gn_pcg2.cuh"
 #include "gn_dense.cuh"
 #include "gn_api.cuh"
 #include "gn_track_api.cuh"

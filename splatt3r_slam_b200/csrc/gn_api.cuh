@@ -99,7 +99,72 @@ inline int launch_edge_blocks(const b200slam_gn_params *p, const BuildConsts &C,
   return rc;
 }
 
-// Large graphs: block-Jacobi PCG on the edge blocks (gn_pcg.cuh), one cooperative launch.
+static int g_solver_mode = -1;  // b200slam_gn_set_solver: -1 = B200SLAM_GN_SOLVER / auto
+
+// Pose adjacency lists [cnt M | ptr M+1 | list 2E] at the head of the L.pcg region (after its 256-byte control
+// block), built once per call (State::adj_ready) and shared by both PCG solvers.
+struct AdjBufs {
+  int *cnt, *ptr, *list;
+};
+inline AdjBufs adj_bufs(char *ws, const Layout &L, int M) {
+  int *ints = reinterpret_cast<int *>(ws + L.pcg + 256);
+  return AdjBufs{ints, ints + M, ints + 2 * M + 1};
+}
+inline int launch_adjacency(const int64_t *ii_row, const int64_t *jj_row, int E, int M, const AdjBufs &A,
+                            const State *state, cudaStream_t st) {
+  const int tb = 128, nb = (M + tb - 1) / tb;
+  adj_count_kernel<<<nb, tb, 0, st>>>(ii_row, jj_row, E, M, A.cnt, state);
+  adj_scan_kernel<<<1, 32, 0, st>>>(A.cnt, M, A.ptr, state);
+  adj_fill_kernel<<<nb, tb, 0, st>>>(ii_row, jj_row, E, M, A.ptr, A.list, state);
+  return (int)cudaGetLastError();
+}
+
+// Default for large graphs: pipelined PCG (gn_pcg2.cuh), one cooperative launch.  Returns 1 when the graph
+// does not qualify (too many poses per warp): the caller then runs the exact solver ungated.
+inline int launch_pcg2(float *Twc, const int64_t *ii_row, const int64_t *jj_row, const double *edge_blocks, int N,
+                       int E, float delta_thresh, float *dx, char *ws, const Layout &L, cudaStream_t st) {
+  State *state = reinterpret_cast<State *>(ws);
+  const int M = N - NUM_FIX, D = 7 * M;
+  const b200dev::Info dev = b200dev::info();
+  if (!dev.coop) return 1;
+  int G = (M + P2_WARPS - 1) / P2_WARPS;
+  if (G > dev.num_sms) G = dev.num_sms;
+  if (G > P2_MAX_CTAS) G = P2_MAX_CTAS;
+  int P = (M + G * P2_WARPS - 1) / (G * P2_WARPS);
+  if (P > P2_MAX_P) return 1;
+  const size_t fixed = (size_t)P2_WARPS * P * P2_POSE_DOUBLES * sizeof(double);
+  if (fixed + 64 * (49 * sizeof(double) + sizeof(int)) > (size_t)P2_SMEM_BYTES) return 1;
+  int blocks_cap = (int)(((size_t)P2_SMEM_BYTES - fixed) / (49 * sizeof(double) + sizeof(int)));
+  char *base = ws + L.pcg2;
+  Pcg2Bufs B;
+  const AdjBufs A = adj_bufs(ws, L, M);
+  B.adj_ptr = A.ptr;
+  B.adj_list = A.list;
+  B.xch = reinterpret_cast<double *>(base);
+  B.part = reinterpret_cast<double *>(base + align256((size_t)2 * D * sizeof(double)));
+  B.tags = reinterpret_cast<unsigned *>(base + align256((size_t)2 * D * sizeof(double)) +
+                                        align256((size_t)2 * P2_MAX_CTAS * 2 * sizeof(double)));
+  static const int env_max = getenv("B200SLAM_GN_PCG_MAXIT") ? atoi(getenv("B200SLAM_GN_PCG_MAXIT")) : 0;
+  B.max_cg = env_max > 0 ? env_max : 400;
+  B.tol2 = 1e-24;       // recursive (r, D^-1 r) relative to its initial value: 1e-12 in norm
+  B.true_tol2 = 1e-20;  // the same for the true residual of the returned x: 1e-10 in norm
+  int rc = (int)cudaMemsetAsync(B.tags, 0, (size_t)2 * P2_MAX_CTAS * sizeof(unsigned), st);
+  if (rc) return rc;
+  rc = launch_adjacency(ii_row, jj_row, E, M, A, state, st);
+  if (rc) return rc;
+  static b200dev::Once attr;
+  if (attr.first()) {
+    cudaError_t err = cudaFuncSetAttribute(pcg2_solve_retract_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                           P2_SMEM_BYTES);
+    if (err != cudaSuccess) { attr.retry(); return (int)err; }
+  }
+  void *args[] = {&Twc, &ii_row, &jj_row, &edge_blocks, &N, &E, &P, &blocks_cap, &B, &delta_thresh, &dx, &state};
+  return (int)cudaLaunchCooperativeKernel((const void *)pcg2_solve_retract_kernel, dim3(G), dim3(P2_THREADS), args,
+                                          (size_t)P2_SMEM_BYTES, st);
+}
+
+// First-generation PCG (gn_pcg.cuh, solver mode "pcg1"): three counter barriers per CG iteration; kept as the
+// A/B baseline of the pipelined one.
 inline int launch_pcg(float *Twc, const int64_t *ii_row, const int64_t *jj_row, const double *edge_blocks, int N,
                       int E, float delta_thresh, float *dx, char *ws, const Layout &L, cudaStream_t st) {
   State *state = reinterpret_cast<State *>(ws);
@@ -110,10 +175,9 @@ inline int launch_pcg(float *Twc, const int64_t *ii_row, const int64_t *jj_row, 
   PcgBufs B;
   B.bar = reinterpret_cast<unsigned *>(base);
   B.flag = reinterpret_cast<int *>(base + 64);
-  int *ints = reinterpret_cast<int *>(base + 256);
-  int *cnt = ints;
-  B.adj_ptr = ints + M;
-  B.adj_list = ints + 2 * M + 1;
+  const AdjBufs A = adj_bufs(ws, L, M);
+  B.adj_ptr = A.ptr;
+  B.adj_list = A.list;
   double *dbl = reinterpret_cast<double *>(base + 256 + align256((2 * (size_t)M + 2 + 2 * (size_t)E) * sizeof(int)));
   B.Minv = dbl;
   B.b = dbl + (size_t)49 * M;
@@ -121,11 +185,7 @@ inline int launch_pcg(float *Twc, const int64_t *ii_row, const int64_t *jj_row, 
   B.r = B.x + D;
   B.p = B.r + D;
   B.part = B.p + D;
-  const int tb = 128, nb = (M + tb - 1) / tb;
-  adj_count_kernel<<<nb, tb, 0, st>>>(ii_row, jj_row, E, M, cnt);
-  adj_scan_kernel<<<1, 32, 0, st>>>(cnt, M, B.adj_ptr);
-  adj_fill_kernel<<<nb, tb, 0, st>>>(ii_row, jj_row, E, M, B.adj_ptr, B.adj_list);
-  rc = (int)cudaGetLastError();
+  rc = launch_adjacency(ii_row, jj_row, E, M, A, state, st);
   if (rc) return rc;
   const int num_sms = b200dev::info().num_sms;
   int grid = (M + PCG_WARPS - 1) / PCG_WARPS;
@@ -139,8 +199,9 @@ inline int launch_pcg(float *Twc, const int64_t *ii_row, const int64_t *jj_row, 
 }
 
 // Graphs beyond the single-CTA solver: exact tiled Cholesky on all SMs (gn_dense.cuh), one cooperative launch.
+// gated != 0: the launches are no-ops unless the pipelined PCG in front of them gave up (State::pcg_bad).
 inline int launch_dense(float *Twc, const int64_t *ii_row, const int64_t *jj_row, const double *edge_blocks, int N,
-                        int E, float delta_thresh, float *dx, char *ws, const Layout &L, cudaStream_t st) {
+                        int E, float delta_thresh, float *dx, char *ws, const Layout &L, cudaStream_t st, int gated) {
   State *state = reinterpret_cast<State *>(ws);
   int M = N - NUM_FIX, D = 7 * M;
   DenseBufs B;
@@ -154,7 +215,7 @@ inline int launch_dense(float *Twc, const int64_t *ii_row, const int64_t *jj_row
         (size_t)49 * M + D;
   int rc = (int)cudaMemsetAsync(ws + L.dense_ctrl, 0, 256, st);
   if (rc) return rc;
-  assemble_kernel<<<M, 256, 0, st>>>(ii_row, jj_row, edge_blocks, E, D, B.A, B.b, state);
+  assemble_kernel<<<M, 256, 0, st>>>(ii_row, jj_row, edge_blocks, E, D, B.A, B.b, state, gated);
   rc = (int)cudaGetLastError();
   if (rc) return rc;
   static b200dev::PerDeviceInt grid_cache;  // all co-resident: SMs x resident CTAs per SM (2 with 68 KB of shared memory each)
@@ -170,7 +231,7 @@ inline int launch_dense(float *Twc, const int64_t *ii_row, const int64_t *jj_row
     if (per_sm < 1) return B200SLAM_EINVAL;
     grid_ctas = num_sms * per_sm;
   }
-  void *args[] = {&Twc, &B, &N, &D, &delta_thresh, &dx, &state};
+  void *args[] = {&Twc, &B, &N, &D, &delta_thresh, &dx, &state, &gated};
   return (int)cudaLaunchCooperativeKernel((const void *)dense_solve_retract_kernel, dim3(grid_ctas), dim3(DENSE_THREADS),
                                           args, smem, st);
 }
@@ -181,13 +242,26 @@ inline int launch_solve(float *Twc, const int64_t *ii_row, const int64_t *jj_row
   State *state = reinterpret_cast<State *>(ws);
   const int M = N - NUM_FIX, D = 7 * M, Dp = D < 32 ? 32 : D;
   if (D > PACKED_MAX_D) {
-    // exact tiled Cholesky by default; B200SLAM_GN_PCG=1 selects the matrix-free PCG (well-connected huge graphs)
-    static const bool use_pcg = getenv("B200SLAM_GN_PCG") != nullptr;
-    return use_pcg ? launch_pcg(Twc, ii_row, jj_row, edge_blocks, N, E, delta_thresh, dx, ws, L, st)
-                   : launch_dense(Twc, ii_row, jj_row, edge_blocks, N, E, delta_thresh, dx, ws, L, st);
+    // Default ("auto"): pipelined PCG with the exact tiled Cholesky enqueued behind it as a gated fallback.
+    // B200SLAM_GN_SOLVER=dense | pcg1 | auto, or b200slam_gn_set_solver(), selects (A/B aid).
+    static const int env_mode = [] {
+      const char *e = getenv("B200SLAM_GN_SOLVER");
+      if (e && !strcmp(e, "dense")) return 1;
+      if (e && !strcmp(e, "pcg1")) return 2;
+      return 0;
+    }();
+    const int mode = g_solver_mode >= 0 ? g_solver_mode : env_mode;
+    if (mode == 2) return launch_pcg(Twc, ii_row, jj_row, edge_blocks, N, E, delta_thresh, dx, ws, L, st);
+    int gated = 0;
+    if (mode == 0) {
+      const int rc = launch_pcg2(Twc, ii_row, jj_row, edge_blocks, N, E, delta_thresh, dx, ws, L, st);
+      if (rc != 0 && rc != 1) return rc;
+      gated = rc == 0;
+    }
+    return launch_dense(Twc, ii_row, jj_row, edge_blocks, N, E, delta_thresh, dx, ws, L, st, gated);
   }
   double *A = reinterpret_cast<double *>(ws + L.A), *rhs = reinterpret_cast<double *>(ws + L.rhs);
-  assemble_kernel<<<M, 256, 0, st>>>(ii_row, jj_row, edge_blocks, E, D, A, rhs, state);
+  assemble_kernel<<<M, 256, 0, st>>>(ii_row, jj_row, edge_blocks, E, D, A, rhs, state, 0);
   int rc = (int)cudaGetLastError();
   if (rc) return rc;
   const size_t smem = solve_smem_bytes(D, Dp, true);
@@ -263,6 +337,29 @@ extern "C" int b200slam_gn_status(const void *workspace, int *iters, int *done, 
   if (iters) *iters = h.iters;
   if (done) *done = h.done;
   if (chol_fail) *chol_fail = h.chol_fail;
+  return 0;
+}
+
+extern "C" int b200slam_gn_set_solver(int mode) {
+  if (mode < -1 || mode > 2) return B200SLAM_EINVAL;
+  g_solver_mode = mode;
+  return 0;
+}
+
+extern "C" int b200slam_gn_solver_status(const void *workspace, int *cg_iters, int *cg_total, int *pcg_bad,
+                                         int *dense_runs, double *cg_rel, double *cg_true_rel, void *stream) {
+  if (!workspace) return B200SLAM_EINVAL;
+  State h;
+  cudaError_t err = cudaMemcpyAsync(&h, workspace, sizeof(State), cudaMemcpyDeviceToHost, (cudaStream_t)stream);
+  if (err != cudaSuccess) return (int)err;
+  err = cudaStreamSynchronize((cudaStream_t)stream);
+  if (err != cudaSuccess) return (int)err;
+  if (cg_iters) *cg_iters = h.cg_iters;
+  if (cg_total) *cg_total = h.cg_total;
+  if (pcg_bad) *pcg_bad = h.pcg_bad;
+  if (dense_runs) *dense_runs = h.dense_runs;
+  if (cg_rel) *cg_rel = h.cg_rel;
+  if (cg_true_rel) *cg_true_rel = h.cg_true_rel;
   return 0;
 }
 

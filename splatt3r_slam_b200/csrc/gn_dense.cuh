@@ -242,8 +242,10 @@ __device__ __forceinline__ void dense_trail_compute(const DenseBufs &B, int D, i
 }
 
 __global__ void __launch_bounds__(DENSE_THREADS, 2)
-dense_solve_retract_kernel(float *Twc, DenseBufs B, int N, int D, float delta_thresh, float *dx, State *state) {
-  if (state->done) return;  // written only at the end of an earlier launch: uniform over the grid
+dense_solve_retract_kernel(float *Twc, DenseBufs B, int N, int D, float delta_thresh, float *dx, State *state,
+                           int gated) {
+  // both flags are written only by earlier launches: uniform over the grid
+  if (state->done || (gated && !state->pcg_bad)) return;
   extern __shared__ __align__(16) double dsm[];
   double *As = dsm, *Bs = dsm + DT * GLD, *v0 = dsm + 2 * DT * GLD;
   __shared__ int fail;
@@ -443,7 +445,10 @@ dense_solve_retract_kernel(float *Twc, DenseBufs B, int N, int D, float delta_th
       grid_barrier(B.bar, gen);
     }
   }
-  if (cta == 0) finish_update(ok, B.x, fin_scratch, D, N, Twc, dx, delta_thresh, state);
+  if (cta == 0) {
+    if (tid == 0) state->dense_runs += 1;
+    finish_update(ok, B.x, fin_scratch, D, N, Twc, dx, delta_thresh, state);
+  }
 }
 
 }  // namespace b200gn

@@ -36,7 +36,8 @@ struct PcgBufs {
 
 // ---- adjacency (three tiny launches; O(M*E) scans, ~40 us at M = 1023, E = 8192) -------------------
 __global__ void adj_count_kernel(const int64_t *__restrict__ ii_row, const int64_t *__restrict__ jj_row, int E, int M,
-                                 int *__restrict__ cnt) {
+                                 int *__restrict__ cnt, const State *__restrict__ state) {
+  if (state->adj_ready || state->done) return;  // built once per call
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= M) return;
   const int row = r + NUM_FIX;
@@ -44,7 +45,8 @@ __global__ void adj_count_kernel(const int64_t *__restrict__ ii_row, const int64
   for (int e = 0; e < E; e++) c += ((int)ii_row[e] == row) + ((int)jj_row[e] == row);
   cnt[r] = c;
 }
-__global__ void adj_scan_kernel(const int *__restrict__ cnt, int M, int *__restrict__ ptr) {
+__global__ void adj_scan_kernel(const int *__restrict__ cnt, int M, int *__restrict__ ptr, const State *__restrict__ state) {
+  if (state->adj_ready || state->done) return;
   // single thread: M <= a few thousand
   if (blockIdx.x == 0 && threadIdx.x == 0) {
     int s = 0;
@@ -53,7 +55,8 @@ __global__ void adj_scan_kernel(const int *__restrict__ cnt, int M, int *__restr
   }
 }
 __global__ void adj_fill_kernel(const int64_t *__restrict__ ii_row, const int64_t *__restrict__ jj_row, int E, int M,
-                                const int *__restrict__ ptr, int *__restrict__ list) {
+                                const int *__restrict__ ptr, int *__restrict__ list, const State *__restrict__ state) {
+  if (state->adj_ready || state->done) return;
   const int r = blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= M) return;
   const int row = r + NUM_FIX;
@@ -278,7 +281,12 @@ pcg_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const i
     }
   }
   grid_barrier(B.bar, gen);  // x complete
-  if (blockIdx.x == 0 && tid == 0) { state->cg_iters = cg_it; state->cg_rel = rz0 > 0.0 ? rz_last / rz0 : 0.0; }
+  if (blockIdx.x == 0 && tid == 0) {
+    state->cg_iters = cg_it;
+    state->cg_total += cg_it;
+    state->cg_rel = rz0 > 0.0 ? rz_last / rz0 : 0.0;
+    state->adj_ready = 1;
+  }
   if (blockIdx.x == 0) finish_update(ok, B.x, fin_scratch, D, N, Twc, dx, delta_thresh, state);
 }
 

@@ -95,8 +95,8 @@ __device__ inline void finalize_edge(const float *Twc, const int64_t *ii_row, co
 __global__ void __launch_bounds__(256)
 assemble_kernel(const int64_t *__restrict__ ii_row, const int64_t *__restrict__ jj_row,
                 const double *__restrict__ edge_blocks, int E, int D, double *__restrict__ A,
-                double *__restrict__ rhs, const State *__restrict__ state) {
-  if (state->done) return;
+                double *__restrict__ rhs, const State *__restrict__ state, int gated) {
+  if (state->done || (gated && !state->pcg_bad)) return;
   const int r = blockIdx.x;
   double *strip = A + (size_t)7 * r * D;
   for (int t = threadIdx.x; t < 7 * D; t += blockDim.x) strip[t] = 0.0;

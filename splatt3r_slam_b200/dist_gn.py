@@ -5,10 +5,13 @@ directed edges split into contiguous ranges, poses/pointmaps replicated.
 Per iteration, on every rank:
   1. stage 1+2 on the rank's own edges -> rows [e0, e0+Ec) of `edge_blocks` (E,56) fp64
      (= [H_jj | g_j] per edge, all other rows zero)                     [b200slam_gn_edge_blocks]
-  2. ONE collective: allreduce(sum) of `edge_blocks` over NCCL/NVLink.  Every row is non-zero on
-     exactly one rank, so the sum is exact (x + 0 + ... + 0) and bit-identical on all ranks
-     whatever the reduction order — the replicated solve below therefore stays in lock-step.
-  3. replicated assembly + fp64 Cholesky + retraction + ||dx|| test      [b200slam_gn_solve_retract]
+  2. ONE collective: all-gather of the ranks' row ranges of `edge_blocks` over NCCL/NVLink (rows are
+     disjoint, so nothing is summed: every rank ends with bit-identical blocks and the replicated
+     solve below stays in lock-step).  Equal shards use all_gather_into_tensor in place; ragged
+     shards (E % world != 0) a padded one.
+  3. replicated solve + retraction + ||dx|| test                         [b200slam_gn_solve_retract]
+     (large graphs: pipelined PCG on the edge blocks, well under a millisecond at N = 1024, so
+     replicating it costs less than one extra collective per CG iteration would)
 No other exchange: the matcher shards by pair with no collective at all.
 
 The compute hooks are injectable so the protocol can be exercised on CPU tensors with the gloo
@@ -79,15 +82,22 @@ def gauss_newton_sharded(prm, Twc, Xs, Cs, K, ii, jj, idx_shard, valid_shard, Q_
         hooks = CudaHooks(prm, N, E, n, Twc.device)
     edge_blocks = torch.zeros((E, 56), dtype=torch.float64, device=Twc.device)
     dx = torch.zeros((N - 1, 7), dtype=torch.float32, device=Twc.device)
+    even = E % world == 0
+    if world > 1 and not even:  # ragged shards: gather through a padded (world, Emax, 56) buffer
+        Emax = (E + world - 1) // world
+        pad = torch.zeros((world, Emax, 56), dtype=torch.float64, device=Twc.device)
+        spans = [shard_range(E, r, world) for r in range(world)]
     for _ in range(max_iter):
-        # rows of other shards must be zero before the sum (this rank's rows are overwritten)
-        if e0 > 0:
-            edge_blocks[:e0].zero_()
-        if e0 + Ec < E:
-            edge_blocks[e0 + Ec:].zero_()
         hooks.edge_blocks(Twc, Xs, Cs, K, ii_row, jj_row, idx_shard, valid_shard, Q_shard, e0, Ec, edge_blocks)
         if world > 1:
-            dist.all_reduce(edge_blocks, op=dist.ReduceOp.SUM, group=group)
+            if even:  # in place: rank r's rows are already at their final position
+                dist.all_gather_into_tensor(edge_blocks, edge_blocks[e0:e0 + Ec], group=group)
+            else:
+                pad[rank, :Ec].copy_(edge_blocks[e0:e0 + Ec])
+                dist.all_gather_into_tensor(pad.view(world * Emax, 56), pad[rank].clone(), group=group)
+                for r, (s0, sc) in enumerate(spans):
+                    if r != rank:
+                        edge_blocks[s0:s0 + sc].copy_(pad[r, :sc])
         hooks.solve_retract(Twc, ii_row, jj_row, edge_blocks, delta_thresh, dx)
     return dx
 

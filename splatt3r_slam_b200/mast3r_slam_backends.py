@@ -46,6 +46,9 @@ def _load():
     lib.b200slam_gn_solve_retract.argtypes = [vp] * 4 + [i, i, i, f, vp, vp, sz, vp]
     lib.b200slam_gn_reset.argtypes = [vp, sz, vp]
     lib.b200slam_gn_status.argtypes = [vp, ctypes.POINTER(i), ctypes.POINTER(i), ctypes.POINTER(i), vp]
+    D = ctypes.POINTER(ctypes.c_double)
+    lib.b200slam_gn_solver_status.argtypes = [vp] + [ctypes.POINTER(i)] * 4 + [D, D, vp]
+    lib.b200slam_gn_set_solver.argtypes = [i]
     lib.b200slam_gauss_newton.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_gauss_newton_ids.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_edge_rows.argtypes = [vp, vp, i, vp, vp, sz, vp]
@@ -60,7 +63,7 @@ def _load():
     lib.b200slam_match_workspace_bytes.restype = sz
     lib.b200slam_match.argtypes = [vp] * 4 + [i] + [vp] * 3 + [i] * 5 + [f, f, f, i, i, vp, sz, vp]
     for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "gn_build_blocks",
-                 "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gauss_newton",
+                 "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gn_solver_status", "gn_set_solver", "gauss_newton",
                  "gauss_newton_ids", "gauss_newton_twoway", "edge_rows", "match", "track_ray_dist", "track_calib", "track_status"):
         getattr(lib, "b200slam_" + name).restype = i
     return lib
@@ -381,8 +384,35 @@ def gn_build_blocks(prm, Twc, Xs, Cs, K, ii, jj, idx, valid, Q):
     return Hs, gs
 
 
+def _ws_of(device):
+    device = torch.device(device)
+    index = device.index if device.index is not None else torch.cuda.current_device()
+    return _workspaces[(device.type, index)]
+
+
 def gn_status(device):
-    return gn_status_ws(_workspaces[(device.type, device.index)])
+    return gn_status_ws(_ws_of(device))
+
+
+SOLVERS = {"default": -1, "auto": 0, "dense": 1, "pcg1": 2}
+
+
+def gn_set_solver(name):
+    """Large-graph solver selection (process-wide): 'default' | 'auto' | 'dense' | 'pcg1'."""
+    _check(_lib.b200slam_gn_set_solver(SOLVERS[name]), "gn_set_solver")
+
+
+def gn_solver_status(ws):
+    """Large-graph solver diagnostics of the last GN call on workspace `ws` (a device, or the uint8 tensor)."""
+    if not isinstance(ws, torch.Tensor):
+        ws = _ws_of(ws)
+    v = [ctypes.c_int() for _ in range(4)]
+    rel, true_rel = ctypes.c_double(), ctypes.c_double()
+    _check(_lib.b200slam_gn_solver_status(ws.data_ptr(), *[ctypes.byref(x) for x in v], ctypes.byref(rel),
+                                          ctypes.byref(true_rel),
+                                          torch.cuda.current_stream(ws.device).cuda_stream), "gn_solver_status")
+    return dict(cg_iters=v[0].value, cg_total=v[1].value, pcg_bad=v[2].value, dense_runs=v[3].value,
+                cg_rel=rel.value, cg_true_rel=true_rel.value)
 
 
 def gn_status_ws(ws):
