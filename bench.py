@@ -161,6 +161,7 @@ def main():
     ap.add_argument("--workload", default="tracker")
     ap.add_argument("--kfs", type=int, default=32)
     ap.add_argument("--edges", type=int, default=128, help="directed edges for --workload graph")
+    ap.add_argument("--kind", default="rays", choices=["rays", "calib"], help="residual model for --workload graph")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.impl == "reference":

@@ -64,6 +64,34 @@ class CudaHooks:
         return self.be.gn_status_ws(self.ws)
 
 
+class EdgeBlockGather:
+    """The one collective of an iteration: every rank contributes rows [e0, e0+Ec) of the (E,56) fp64
+    edge-block array and ends with all of them (disjoint rows: nothing is summed)."""
+
+    def __init__(self, E, rank, world, device, group=None):
+        self.E, self.rank, self.world, self.group = E, rank, world, group
+        self.e0, self.Ec = shard_range(E, rank, world)
+        self.even = E % world == 0
+        if world > 1 and not self.even:  # ragged shards: gather through a padded (world, Emax, 56) buffer
+            self.Emax = (E + world - 1) // world
+            self.pad = torch.zeros((world, self.Emax, 56), dtype=torch.float64, device=device)
+            self.mine = torch.zeros((self.Emax, 56), dtype=torch.float64, device=device)
+            self.spans = [shard_range(E, r, world) for r in range(world)]
+
+    def run(self, edge_blocks):
+        if self.world == 1:
+            return
+        e0, Ec = self.e0, self.Ec
+        if self.even:  # in place: this rank's rows are already at their final position
+            dist.all_gather_into_tensor(edge_blocks, edge_blocks[e0:e0 + Ec], group=self.group)
+            return
+        self.mine[:Ec].copy_(edge_blocks[e0:e0 + Ec])
+        dist.all_gather_into_tensor(self.pad.view(self.world * self.Emax, 56), self.mine, group=self.group)
+        for r, (s0, sc) in enumerate(self.spans):
+            if r != self.rank:
+                edge_blocks[s0:s0 + sc].copy_(self.pad[r, :sc])
+
+
 def gauss_newton_sharded(prm, Twc, Xs, Cs, K, ii, jj, idx_shard, valid_shard, Q_shard, max_iter, delta_thresh,
                          group=None, hooks=None, rows=None):
     """Edge-sharded GN.  Twc (N,8) is updated in place on every rank (identically).
@@ -82,112 +110,9 @@ def gauss_newton_sharded(prm, Twc, Xs, Cs, K, ii, jj, idx_shard, valid_shard, Q_
         hooks = CudaHooks(prm, N, E, n, Twc.device)
     edge_blocks = torch.zeros((E, 56), dtype=torch.float64, device=Twc.device)
     dx = torch.zeros((N - 1, 7), dtype=torch.float32, device=Twc.device)
-    even = E % world == 0
-    if world > 1 and not even:  # ragged shards: gather through a padded (world, Emax, 56) buffer
-        Emax = (E + world - 1) // world
-        pad = torch.zeros((world, Emax, 56), dtype=torch.float64, device=Twc.device)
-        spans = [shard_range(E, r, world) for r in range(world)]
+    gather = EdgeBlockGather(E, rank, world, Twc.device, group)
     for _ in range(max_iter):
         hooks.edge_blocks(Twc, Xs, Cs, K, ii_row, jj_row, idx_shard, valid_shard, Q_shard, e0, Ec, edge_blocks)
-        if world > 1:
-            if even:  # in place: rank r's rows are already at their final position
-                dist.all_gather_into_tensor(edge_blocks, edge_blocks[e0:e0 + Ec], group=group)
-            else:
-                pad[rank, :Ec].copy_(edge_blocks[e0:e0 + Ec])
-                dist.all_gather_into_tensor(pad.view(world * Emax, 56), pad[rank].clone(), group=group)
-                for r, (s0, sc) in enumerate(spans):
-                    if r != rank:
-                        edge_blocks[s0:s0 + sc].copy_(pad[r, :sc])
+        gather.run(edge_blocks)
         hooks.solve_retract(Twc, ii_row, jj_row, edge_blocks, delta_thresh, dx)
     return dx
-
-
-def bench_graph(args, rank, world, local):
-    """bench.py --workload graph: global optimisation over a keyframe graph (BASELINE.json
-    configs[2]/[3] shape), E directed edges sharded over `world` GPUs, 10 GN iterations per step
-    (delta_thresh = 0), strong scaling.  Returns the JSON line (rank 0) or None."""
-    import json
-    import os
-    from . import mast3r_slam_backends as be
-    from . import synthetic
-    dev = torch.device("cuda", local)
-    N, E = args.kfs, args.edges
-    n = 384 * 512
-    e0, Ec = shard_range(E, rank, world)
-    # generated on the device, this rank's edge shard only (configs[3] is 21 GB of per-edge arrays)
-    g = synthetic.make_graph_device(7, N, E // 2, 384, 512, dev, edge_range=(e0, e0 + Ec))
-    G = {k: g[k] for k in ("Twc", "Xs", "Cs", "ii", "jj")}
-    idx_s, val_s, Q_s = g["idx_ii2jj"], g["valid_match"], g["Q"]
-    prm = be.make_params(0, 0.003, 10.0, 0.0, 1.5)
-    rows = be.edge_rows(G["ii"], G["jj"])
-    hooks = CudaHooks(prm, N, E, n, dev)
-    iters = 10
-
-    def step():
-        T = G["Twc"].clone()
-        be._check(be._lib.b200slam_gn_reset(hooks.ws.data_ptr(), hooks.nbytes, hooks._stream()), "gn_reset")
-        gauss_newton_sharded(prm, T, G["Xs"], G["Cs"], None, G["ii"], G["jj"], idx_s, val_s, Q_s, iters, 0.0,
-                             hooks=hooks, rows=rows)
-        return T
-
-    for _ in range(max(3, args.warmup)):
-        step()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    sampler = None
-    if rank == 0:
-        try:  # SM clocks / throttle reasons under load (bench.py's sampler; absent when used outside the bench)
-            from bench import ClockSampler
-            sampler = ClockSampler(local)
-            sampler.start()
-        except Exception:
-            sampler = None
-    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    a.record()
-    for _ in range(args.steps):
-        T = step()
-    b.record()
-    if world > 1:
-        dist.barrier()
-    torch.cuda.synchronize()
-    if sampler is not None:
-        sampler.stop_flag = True
-        sampler.join(timeout=10)
-    t = torch.tensor([a.elapsed_time(b)], dtype=torch.float64, device=dev)
-    if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = t.item()
-    # all ranks must hold bit-identical poses (replicated solve in lock-step)
-    chk = T.clone()
-    if world > 1:
-        dist.broadcast(chk, src=0)
-    flag = torch.tensor([int(torch.equal(chk, T))], device=dev)
-    if world > 1:
-        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
-    same = bool(flag.item())
-    if rank != 0:
-        return None
-    try:
-        peak = float(json.load(open(os.path.join(os.path.dirname(os.path.dirname(__file__)), "MEASURED_PEAKS.json")))["hbm_gbs"])
-        src = "measured"
-    except Exception:
-        peak, src = 6650.0, "fallback"
-    per_iter_ms = ms / (args.steps * iters)
-    alg_bytes = (E * (45.0 * n + 840.0)) / world  # per GPU per iteration (SURVEY 8d: 45 B/point + 840 B/edge)
-    ach = alg_bytes / (per_iter_ms * 1e-3) / 1e9
-    return {
-        "metric": "gn_iters_per_s", "value": args.steps * iters / (ms * 1e-3), "unit": "iters/s", "n_gpus": world,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"global_opt gauss_newton_rays N={N} keyframes E={E} directed edges 512x384, 10 iters/step",
-                   "sharding": "contiguous edge ranges, one NCCL allreduce of (E,56) fp64 per iteration",
-                   "l2": f"per-iteration working set {E * 45.0 * n / world / 1e6:.0f} MB per GPU"},
-        "roofline": {"bound": "hbm", "kernel": "gn build (whole iteration incl. solve + allreduce)", "achieved": ach,
-                     "peak": peak, "unit": "GB/s", "frac": ach / peak,
-                     # build kernel at N=32/E=128 from profiles/r01b_ncu_graph_summary.txt (658.8 MB read per launch;
-                     # keyframe pointmaps are re-used from L2 across edges); other sizes not captured
-                     "traffic": 658.8e6 if (N, E, world) == (32, 128, 1) else None, "peak_source": src},
-        "ranks_bit_identical": same, "gpu_launches": args.steps * iters * 4,
-        "clocks": sampler.result() if sampler is not None else None,
-    }
