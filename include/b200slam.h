@@ -157,9 +157,11 @@ int b200slam_gn_set_solver(int mode);
  * reference's counterpart is SparseBlock::solve's solver.info() (gn_kernels.cu:141-149), which it does not
  * expose.  cg_iters / cg_rel / cg_true_rel: iterations and relative (r, D^-1 r) — recursive and true — of
  * the last pipelined-PCG solve; cg_total: PCG iterations summed over the call; pcg_bad: the PCG gave up and
- * the exact tiled Cholesky took over; dense_runs: how many exact solves the call executed. */
+ * the exact tiled Cholesky took over; dense_runs: how many exact solves the call executed; stamps_ns[4]
+ * (optional): %globaltimer at {start, set-up done, iterations done, end} of the last solver kernel. */
 int b200slam_gn_solver_status(const void *workspace, int *cg_iters, int *cg_total, int *pcg_bad,
-                              int *dense_runs, double *cg_rel, double *cg_true_rel, void *stream);
+                              int *dense_runs, double *cg_rel, double *cg_true_rel,
+                              unsigned long long *stamps_ns, void *stream);
 
 /* Whole driver: replaces gauss_newton_{rays,calib,points}_cuda (gn_kernels.cu:1139-1227,
  * :1545-1637, :724-810) for a single GPU.  Enqueues max_iter iterations with no host

@@ -347,7 +347,8 @@ extern "C" int b200slam_gn_set_solver(int mode) {
 }
 
 extern "C" int b200slam_gn_solver_status(const void *workspace, int *cg_iters, int *cg_total, int *pcg_bad,
-                                         int *dense_runs, double *cg_rel, double *cg_true_rel, void *stream) {
+                                         int *dense_runs, double *cg_rel, double *cg_true_rel,
+                                         unsigned long long *stamps_ns, void *stream) {
   if (!workspace) return B200SLAM_EINVAL;
   State h;
   cudaError_t err = cudaMemcpyAsync(&h, workspace, sizeof(State), cudaMemcpyDeviceToHost, (cudaStream_t)stream);
@@ -360,6 +361,8 @@ extern "C" int b200slam_gn_solver_status(const void *workspace, int *cg_iters, i
   if (dense_runs) *dense_runs = h.dense_runs;
   if (cg_rel) *cg_rel = h.cg_rel;
   if (cg_true_rel) *cg_true_rel = h.cg_true_rel;
+  if (stamps_ns)
+    for (int k = 0; k < 4; k++) stamps_ns[k] = h.t[k];
   return 0;
 }
 
