@@ -7,9 +7,11 @@ function uses are restated on the (t, q_xyzw, s) 8-vector: inv, mul, act (lietor
 156-165) and retr = Exp(tau) * T through the C oracle's retraction (oracle_gn_solve.c, pinned against
 the reference CUDA build's pose_retr_kernel).
 
-PARITY UNPINNED for this function: the reference's tracker cannot be imported here (lietorch), and it
-has no golden vectors.  What is pinned: the Sim3 helpers (shared with the GN oracle) and, in
-tests/test_oracle_golden.py, that this restatement reduces the cost and recovers a known relative pose.
+PARITY PINNED against the reference's own tracker.py: oracle/build_lietorch.py builds the reference's
+lietorch and byte-compiles its drivers; tests/golden/make_golden_drivers.py ran
+FrameTracker.opt_pose_ray_dist_sim3 / opt_pose_calib_sim3 with them and committed the poses
+(tests/golden/drivers_64x48.npz); tests/test_drivers_golden.py holds this restatement to 1e-5 of those
+(measured <= 1.7e-6) and, where oracle/_ref is present, to the live reference tracker on fresh seeds.
 Only tests/, __graft_entry__.smoke() and bench.py's CPU baselines may import this module."""
 import math
 

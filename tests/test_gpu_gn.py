@@ -101,16 +101,16 @@ def test_vs_oracle_and_reference(backend, ref_backend, name, N, Eu, h, w):
                              prm.C_thresh, prm.Q_thresh, prm.height, prm.width, prm.pixel_border, prm.z_eps)
     for e in range(2 * Eu):  # per edge: every Hessian block within 1e-5 of that block's scale
         assert rel(Hs[:, e].cpu(), Ho[:, e]) < RTOL, e
-        assert rel(gs[:, e].cpu(), go[:, e]) < 5 * RTOL, e
+        assert rel(gs[:, e].cpu(), go[:, e]) < RTOL, e
     Tb = G["Twc"].clone()
     run(backend, name, Tb, G, h, w, 5, 0.0)
     To = g["Twc"].clone()
     run(oracle, name, To, g, h, w, 5, 0.0)
-    assert (Tb.cpu() - To).abs().max().item() < 2e-5
+    assert rel(Tb.cpu(), To) < RTOL
     if ref_backend is not None:
         Tr = G["Twc"].clone()
         run(ref_backend, name, Tr, G, h, w, 5, 0.0)
-        assert (Tb - Tr).abs().max().item() < 2e-5
+        assert rel(Tb, Tr) < RTOL
 
 
 def test_early_exit_keeps_reference_iteration_count(backend, golden):
@@ -127,8 +127,10 @@ def test_early_exit_keeps_reference_iteration_count(backend, golden):
     Tb, To = G2["Twc"].clone(), g2["Twc"].clone()
     run(backend, "rays", Tb, G2, 48, 64, 30, 2e-5)
     run(oracle, "rays", To, g2, 48, 64, 30, 2e-5)
+    # the exit test compares ||dx|| (fp32) with the threshold: two correct implementations can straddle it by one
+    # iteration when ||dx|| lands within rounding of delta; the poses must agree to the contract either way
     assert abs(backend.gn_status(dev())["iters"] - oracle._gauss_newton.last_iters) <= 1
-    assert (Tb.cpu() - To).abs().max().item() < 5e-5
+    assert rel(Tb.cpu(), To) < RTOL
 
 
 def test_not_spd_gives_zero_update(backend, golden):

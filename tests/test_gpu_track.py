@@ -1,9 +1,12 @@
 """GPU tier: on-device frame tracker (b200slam_track_ray_dist) against the CPU
 restatement of the reference's FrameTracker.opt_pose_ray_dist_sim3 (oracle/tracker_ref.py) on the same
-seeded problems.  Floating point: poses within 1e-4 absolute, same number of Gauss-Newton steps.  The
-tolerance is set by the REFERENCE side: its normal equations have a condition number of ~1e7 (sigma_dist /
-sigma_ray = 3333, squared) and it factors them in fp32, so its own scale / depth-translation entries carry
-errors of a few 1e-5; the device path sums in fp32 but reduces and factors in fp64."""
+seeded problems.  The restatement is PINNED: tests/golden/drivers_64x48.npz holds the poses the reference's own
+tracker.py produced (with the reference's lietorch), and tests/test_drivers_golden.py checks the restatement against
+them (<= 1.7e-6) and, where oracle/_ref travelled, against the live reference tracker.  Floating point: poses within
+2e-5 absolute on Sim3 data of magnitude <= 1, same number of Gauss-Newton steps.  The bound is set by the REFERENCE
+side: its normal equations have a condition number of ~1e7 (sigma_dist / sigma_ray = 3333, squared) and it forms and
+factors them in fp32 (torch A^T A over 4n rows), so its own result moves by ~1e-5 with the summation order (CPU vs
+CUDA torch); the device path sums in fp32 but reduces and factors in fp64."""
 import pytest
 import torch
 
@@ -11,7 +14,7 @@ from oracle import tracker_ref as tr
 from splatt3r_slam_b200 import synthetic, tracker
 
 pytestmark = pytest.mark.gpu
-TOL = 1e-4
+TOL = 2e-5
 
 
 def run_both(backend, P, **over):
