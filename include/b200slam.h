@@ -51,6 +51,10 @@ int b200slam_refine_matches_f16(const void *D11, const void *D21, const int64_t 
 int b200slam_refine_matches_f32(const float *D11, const float *D21, const int64_t *p1,
                                 int64_t *p1_new, int b, int h, int w, int n, int fdim, int radius,
                                 int dilation_max, void *stream);
+/* double instantiation (the third type AT_DISPATCH_FLOATING_TYPES_AND_HALF covers, matching_kernels.cu:102). */
+int b200slam_refine_matches_f64(const double *D11, const double *D21, const int64_t *p1,
+                                int64_t *p1_new, int b, int h, int w, int n, int fdim, int radius,
+                                int dilation_max, void *stream);
 
 /* Fused match_iterative_proj: replaces the PyTorch glue of splatt3r_slam/matching.py:25-49
  * (prep_for_iter_proj: F.normalize, image.py:5-38 gradients, cat/permute, lin_to_pixel), :52-65

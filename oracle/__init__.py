@@ -63,6 +63,8 @@ def refine_matches(D11, D21, p1, radius, dilation_max):
         fn = lib().oracle_refine_matches_f16
     elif D11.dtype == torch.float32:
         fn = lib().oracle_refine_matches_f32
+    elif D11.dtype == torch.float64:
+        fn = lib().oracle_refine_matches_f64
     else:
         raise TypeError(D11.dtype)
     assert D21.dtype == D11.dtype and D11.is_contiguous() and D21.is_contiguous()

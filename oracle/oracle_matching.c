@@ -224,3 +224,38 @@ void oracle_refine_matches_f32(const float *D11, const float *D21, const int64_t
     p1_new[2 * bq + 1] = v_new;
   }
 }
+
+/* double instantiation of refine_matches_kernel (AT_DISPATCH_FLOATING_TYPES_AND_HALF, matching_kernels.cu:102):
+ * same scan, seed ::cuda::std::numeric_limits<double>::min() = DBL_MIN (:46), `score += a * b` contracted to one
+ * DFMA by nvcc exactly like the float instantiation's FFMA. */
+void oracle_refine_matches_f64(const double *D11, const double *D21, const int64_t *p1,
+                               int64_t *p1_new, int b, int h, int w, int n, int fdim,
+                               int radius, int dilation_max) {
+#pragma omp parallel for schedule(static)
+  for (long bq = 0; bq < (long)b * n; bq++) {
+    const int bi = (int)(bq / n);
+    const double *q = D21 + (size_t)bq * fdim;
+    const double *img = D11 + (size_t)bi * h * w * fdim;
+    int64_t u0 = p1[2 * bq + 0], v0 = p1[2 * bq + 1];
+    double max_score = 2.2250738585072014e-308;
+    int64_t u_new = u0, v_new = v0;
+    for (int d = dilation_max; d > 0; d--) {
+      const int rd = radius * d;
+      const int diam = 2 * rd + 1;
+      for (int i = 0; i < diam; i += d)
+        for (int j = 0; j < diam; j += d) {
+          const int64_t u = u0 - rd + i, v = v0 - rd + j;
+          if (v >= 0 && v < h && u >= 0 && u < w) {
+            const double *cnd = img + ((size_t)v * w + (size_t)u) * fdim;
+            double score = 0.0;
+            for (int k = 0; k < fdim; k++) score = fma(q[k], cnd[k], score);
+            if (score > max_score) { max_score = score; u_new = u; v_new = v; }
+          }
+        }
+      u0 = u_new;
+      v0 = v_new;
+    }
+    p1_new[2 * bq + 0] = u_new;
+    p1_new[2 * bq + 1] = v_new;
+  }
+}

@@ -129,20 +129,23 @@ refine_f16_generic_kernel(const __half *__restrict__ D11, const __half *__restri
   p1_new[2 * bq + 1] = v_new;
 }
 
-// float instantiation: score = fma(q_k, c_k, score) (nvcc contracts the reference's MAC),
-// seed FLT_MIN.
+// float / double instantiations: score = fma(q_k, c_k, score) (nvcc contracts the reference's MAC into one
+// FFMA / DFMA), seed numeric_limits<scalar>::min() = FLT_MIN / DBL_MIN (matching_kernels.cu:46).
+__device__ __forceinline__ float mac_rn(float a, float b, float c) { return __fmaf_rn(a, b, c); }
+__device__ __forceinline__ double mac_rn(double a, double b, double c) { return __fma_rn(a, b, c); }
+template <typename real>
 __global__ void __launch_bounds__(RF_THREADS)
-refine_f32_kernel(const float *__restrict__ D11, const float *__restrict__ D21,
-                  const int64_t *__restrict__ p1, int64_t *__restrict__ p1_new, int h, int w, int n,
-                  int fdim, int radius, int dilation_max) {
+refine_real_kernel(const real *__restrict__ D11, const real *__restrict__ D21,
+                   const int64_t *__restrict__ p1, int64_t *__restrict__ p1_new, int h, int w, int n,
+                   int fdim, int radius, int dilation_max, real seed) {
   const int qi = blockIdx.x * RF_THREADS + threadIdx.x;
   if (qi >= n) return;
   const size_t bq = (size_t)blockIdx.y * n + qi;
-  const float *img = D11 + (size_t)blockIdx.y * h * w * fdim;
-  const float *q = D21 + bq * fdim;
+  const real *img = D11 + (size_t)blockIdx.y * h * w * fdim;
+  const real *q = D21 + bq * fdim;
   long long u0 = p1[2 * bq], v0 = p1[2 * bq + 1];
   long long u_new = u0, v_new = v0;
-  float max_score = 1.17549435e-38f;
+  real max_score = seed;
   for (int d = dilation_max; d > 0; d--) {
     const int rd = radius * d;
     for (int i = -rd; i <= rd; i += d) {
@@ -151,9 +154,9 @@ refine_f32_kernel(const float *__restrict__ D11, const float *__restrict__ D21,
       for (int j = -rd; j <= rd; j += d) {
         const long long v = v0 + j;
         if (v < 0 || v >= h) continue;
-        const float *cand = img + ((size_t)v * w + (size_t)u) * fdim;
-        float s = 0.0f;
-        for (int k = 0; k < fdim; k++) s = __fmaf_rn(__ldg(q + k), __ldg(cand + k), s);
+        const real *cand = img + ((size_t)v * w + (size_t)u) * fdim;
+        real s = 0;
+        for (int k = 0; k < fdim; k++) s = mac_rn(__ldg(q + k), __ldg(cand + k), s);
         if (s > max_score) { max_score = s; u_new = u; v_new = v; }
       }
     }
@@ -242,7 +245,20 @@ extern "C" int b200slam_refine_matches_f32(const float *D11, const float *D21, c
   if (!D11 || !D21 || !p1 || !p1_new) return B200SLAM_EINVAL;
   if (h < 1 || w < 1 || fdim < 0 || radius < 0) return B200SLAM_EINVAL;
   dim3 grid((n + RF_THREADS - 1) / RF_THREADS, b);
-  refine_f32_kernel<<<grid, RF_THREADS, 0, (cudaStream_t)stream>>>(D11, D21, p1, p1_new, h, w, n,
-                                                                   fdim, radius, dilation_max);
+  refine_real_kernel<float><<<grid, RF_THREADS, 0, (cudaStream_t)stream>>>(D11, D21, p1, p1_new, h, w, n, fdim, radius,
+                                                                           dilation_max, 1.17549435e-38f);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200slam_refine_matches_f64(const double *D11, const double *D21, const int64_t *p1,
+                                           int64_t *p1_new, int b, int h, int w, int n, int fdim,
+                                           int radius, int dilation_max, void *stream) {
+  if (b < 0 || n < 0) return B200SLAM_EINVAL;
+  if (b == 0 || n == 0) return B200SLAM_OK;
+  if (!D11 || !D21 || !p1 || !p1_new) return B200SLAM_EINVAL;
+  if (h < 1 || w < 1 || fdim < 0 || radius < 0) return B200SLAM_EINVAL;
+  dim3 grid((n + RF_THREADS - 1) / RF_THREADS, b);
+  refine_real_kernel<double><<<grid, RF_THREADS, 0, (cudaStream_t)stream>>>(D11, D21, p1, p1_new, h, w, n, fdim, radius,
+                                                                            dilation_max, 2.2250738585072014e-308);
   return (int)cudaGetLastError();
 }

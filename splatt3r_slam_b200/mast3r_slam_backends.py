@@ -39,6 +39,7 @@ def _load():
     lib.b200slam_iter_proj_workspace_bytes.restype = sz
     lib.b200slam_refine_matches_f16.argtypes = [vp] * 4 + [i] * 7 + [vp]
     lib.b200slam_refine_matches_f32.argtypes = [vp] * 4 + [i] * 7 + [vp]
+    lib.b200slam_refine_matches_f64.argtypes = [vp] * 4 + [i] * 7 + [vp]
     lib.b200slam_gn_workspace_bytes.argtypes = [i, i, i]
     lib.b200slam_gn_workspace_bytes.restype = sz
     lib.b200slam_gn_build_blocks.argtypes = [P] + [vp] * 9 + [i] * 5 + [vp, vp, vp, sz, vp]
@@ -62,7 +63,7 @@ def _load():
     lib.b200slam_match_workspace_bytes.argtypes = [i] * 5
     lib.b200slam_match_workspace_bytes.restype = sz
     lib.b200slam_match.argtypes = [vp] * 4 + [i] + [vp] * 3 + [i] * 5 + [f, f, f, i, i, vp, sz, vp]
-    for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "gn_build_blocks",
+    for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "refine_matches_f64", "gn_build_blocks",
                  "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gn_solver_status", "gn_set_solver", "gauss_newton",
                  "gauss_newton_ids", "gauss_newton_twoway", "edge_rows", "match", "track_ray_dist", "track_calib", "track_status"):
         getattr(lib, "b200slam_" + name).restype = i
@@ -140,6 +141,8 @@ def refine_matches(D11, D21, p1, radius, dilation_max):
         fn = _lib.b200slam_refine_matches_f16
     elif D11.dtype == torch.float32:
         fn = _lib.b200slam_refine_matches_f32
+    elif D11.dtype == torch.float64:
+        fn = _lib.b200slam_refine_matches_f64
     else:
         raise RuntimeError(f"refine_matches: unsupported descriptor dtype {D11.dtype}")
     ptrs = (_cuda(D11, D11.dtype, "D11"), _cuda(D21, D11.dtype, "D21"), _cuda(p1, torch.int64, "p1"))

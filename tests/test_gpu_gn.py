@@ -218,3 +218,93 @@ def test_large_solve_matches_fp64_dense_solve(backend, N, Eu, h, w, solver):
     ref = -torch.linalg.solve(H, b)
     err = (dx.cpu().double().view(-1) - ref).abs().max().item()
     assert err <= 2e-6 * ref.abs().max().item() + 1e-12, (err, ref.abs().max().item())
+
+
+def _to_dev(g):
+    return {k: (v.to(dev()) if torch.is_tensor(v) else v) for k, v in g.items()}
+
+
+def test_eight_edges_full_size_goes_through_the_one_launch_tail(backend):
+    """N = 5, 4 undirected edges (E = 8) at 384x512: too many points for the persistent kernel, so every iteration
+    is ONE build launch whose last CTA finalizes 8 x 35 = 280 sums with 256 threads (the scratch was sized for 256)."""
+    h, w = 384, 512
+    g = synthetic.make_graph(seed=17, N=5, E_undirected=4, h=h, w=w)
+    G = _to_dev(g)
+    Tb, To = G["Twc"].clone(), g["Twc"].clone()
+    run(backend, "rays", Tb, G, h, w, 3, 0.0)
+    run(oracle, "rays", To, g, h, w, 3, 0.0)
+    assert rel(Tb.cpu(), To) < RTOL
+    assert backend.gn_status(dev())["iters"] == 3
+
+
+def test_no_persist_env_takes_the_per_iteration_path():
+    """B200SLAM_GN_NO_PERSIST=1 (read once per process) in a child process: E = 8 at small n, which the persistent
+    kernel would otherwise take, through build_kernel<KIND, true> + small_tail<256>."""
+    import subprocess
+    import sys
+    code = (
+        "import torch, oracle\n"
+        "from splatt3r_slam_b200 import synthetic\n"
+        "import splatt3r_slam_b200.mast3r_slam_backends as be\n"
+        "g = synthetic.make_graph(seed=23, N=5, E_undirected=4, h=48, w=64)\n"
+        "G = {k: (v.cuda() if torch.is_tensor(v) else v) for k, v in g.items()}\n"
+        "Tb, To = G['Twc'].clone(), g['Twc'].clone()\n"
+        "a = (0.003, 10.0, 0.0, 1.5, 4, 0.0)\n"
+        "be.gauss_newton_rays(Tb, G['Xs'], G['Cs'], G['ii'], G['jj'], G['idx_ii2jj'], G['valid_match'], G['Q'], *a)\n"
+        "oracle.gauss_newton_rays(To, g['Xs'], g['Cs'], g['ii'], g['jj'], g['idx_ii2jj'], g['valid_match'], g['Q'], *a)\n"
+        "err = ((Tb.cpu() - To).abs().max() / To.abs().max()).item()\n"
+        "assert err < 1e-5, err\n"
+        "print('ok', err)\n")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    env = dict(os.environ, B200SLAM_GN_NO_PERSIST="1", PYTHONPATH=root)
+    out = subprocess.run([sys.executable, "-c", code], env=env, cwd=root, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
+
+
+def test_misaligned_views_take_the_scalar_path(backend, golden):
+    """Contiguous views whose storage offset is not a multiple of 16 bytes (4 for the bool mask): the vectorised
+    build must not be used (it would fault with a misaligned address); same poses as the aligned call."""
+    g, G = golden
+    def shifted(t, k):
+        flat = torch.empty(t.numel() + k, dtype=t.dtype, device=t.device)
+        v = flat[k:].view(t.shape)
+        v.copy_(t)
+        return v
+    Ta = G["Twc"].clone()
+    run(backend, "rays", Ta, G, 48, 64, 3, 0.0)
+    Gs = dict(G, Xs=shifted(G["Xs"], 1), Cs=shifted(G["Cs"], 3), idx_ii2jj=shifted(G["idx_ii2jj"], 1),
+              valid_match=shifted(G["valid_match"], 1), Q=shifted(G["Q"], 2))
+    assert Gs["Xs"].data_ptr() % 16 != 0 and Gs["valid_match"].data_ptr() % 4 != 0
+    Tb = G["Twc"].clone()
+    run(backend, "rays", Tb, Gs, 48, 64, 3, 0.0)
+    assert rel(Tb, Ta) < RTOL
+
+
+def test_config3_calib_32_keyframes_128_edges_full_size(backend, ref_backend):
+    """BASELINE.json configs[2] as written: gauss_newton_calib, N = 32, E = 128 directed edges, 512x384.  Per-edge
+    Hessian blocks of a subset of edges against the C oracle (the oracle's build is serial per edge), and the 10
+    iteration loop against the reference's CUDA build when it travelled."""
+    h, w, N, E = 384, 512, 32, 128
+    G = synthetic.make_graph_device(5, N, E // 2, h, w, dev())
+    prm = params(backend, "calib", h, w)
+    Hs, gs = backend.gn_build_blocks(prm, G["Twc"], G["Xs"], G["Cs"], G["K"].to(dev()), G["ii"], G["jj"], G["idx_ii2jj"],
+                                     G["valid_match"], G["Q"])
+    sub = torch.tensor([0, 31, 63, 64, 100, 127])
+    c = lambda t: t.cpu().contiguous()
+    ii_s, jj_s = c(G["ii"])[sub], c(G["jj"])[sub]
+    uniq = torch.unique(torch.cat([ii_s, jj_s]))  # the oracle ranks ids among those it is given: hand it those keyframes only
+    Ho, go = oracle.gn_build(prm.kind, c(G["Twc"])[uniq], c(G["Xs"])[uniq], c(G["Cs"])[uniq], c(G["K"]), ii_s, jj_s,
+                             c(G["idx_ii2jj"][sub.to(dev())]), c(G["valid_match"][sub.to(dev())]), c(G["Q"][sub.to(dev())]),
+                             prm.sigma_a, prm.sigma_b, prm.C_thresh, prm.Q_thresh, prm.height, prm.width,
+                             prm.pixel_border, prm.z_eps)
+    for k, e in enumerate(sub.tolist()):
+        assert rel(Hs[:, e].cpu(), Ho[:, k]) < RTOL, e
+        assert rel(gs[:, e].cpu(), go[:, k]) < RTOL, e
+    Tb = G["Twc"].clone()
+    Gd = dict(G, K=G["K"].to(dev()))
+    run(backend, "calib", Tb, Gd, h, w, 10, 0.0)
+    assert backend.gn_status(dev())["iters"] == 10 and (Tb - G["Twc"]).abs().max() > 1e-4
+    if ref_backend is not None:
+        Tr = G["Twc"].clone()
+        run(ref_backend, "calib", Tr, Gd, h, w, 10, 0.0)
+        assert rel(Tb, Tr) < RTOL

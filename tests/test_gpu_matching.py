@@ -125,6 +125,23 @@ def test_refine_edge_cases(backend):
         assert torch.equal(r.cpu(), r_o), fd
 
 
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float64])
+def test_refine_float_and_double_instantiations(backend, ref_backend, dtype):
+    """The reference dispatches refine_matches over double, float and Half (matching_kernels.cu:102); the drivers only
+    use Half, but a drop-in must take all three: same indices as the oracle and as the reference build."""
+    h, w, fdim, n = 48, 64, 24, 48 * 64
+    g = torch.Generator().manual_seed(5)
+    D11 = torch.nn.functional.normalize(torch.randn(2, h, w, fdim, generator=g, dtype=torch.float64), dim=-1).to(dtype)
+    D21 = torch.nn.functional.normalize(torch.randn(2, n, fdim, generator=g, dtype=torch.float64), dim=-1).to(dtype)
+    p1 = torch.stack([torch.randint(0, w, (2, n), generator=g), torch.randint(0, h, (2, n), generator=g)], -1)
+    (r,) = backend.refine_matches(D11.to(dev()), D21.to(dev()), p1.to(dev()), *RF)
+    (r_o,) = oracle.refine_matches(D11, D21, p1, *RF)
+    assert torch.equal(r.cpu(), r_o) and (r.cpu() != p1).any()
+    if ref_backend is not None:
+        (r_r,) = ref_backend.refine_matches(D11.to(dev()), D21.to(dev()), p1.to(dev()), *RF)
+        assert torch.equal(r, r_r)
+
+
 def test_error_convention(backend):
     x = torch.zeros(1, 8, 8, 18, device=dev())[..., ::2]
     with pytest.raises(RuntimeError, match="must be contiguous"):  # gn.h:5 CHECK_CONTIGUOUS
