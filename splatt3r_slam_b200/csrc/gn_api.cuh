@@ -361,8 +361,10 @@ extern "C" int b200slam_gn_solver_status(const void *workspace, int *cg_iters, i
   if (dense_runs) *dense_runs = h.dense_runs;
   if (cg_rel) *cg_rel = h.cg_rel;
   if (cg_true_rel) *cg_true_rel = h.cg_true_rel;
-  if (stamps_ns)
+  if (stamps_ns) {
     for (int k = 0; k < 4; k++) stamps_ns[k] = h.t[k];
+    for (int k = 0; k < 3; k++) stamps_ns[4 + k] = h.prof[k];
+  }
   return 0;
 }
 

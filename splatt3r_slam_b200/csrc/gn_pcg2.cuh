@@ -86,9 +86,13 @@ __device__ __forceinline__ void p2_publish(const Pcg2Bufs &B, unsigned seq, doub
 __device__ __forceinline__ void p2_wait(const Pcg2Bufs &B, unsigned seq, double &g, double &d) {
   const int lane = threadIdx.x & 31, par = seq & 1, G = gridDim.x;
   double sg = 0.0, sd = 0.0;
-  // Spin with RELAXED loads and fence once: ld.acquire.gpu compiles to LDG.STRONG + CCTL.IVALL (an L1
-  // invalidate-all per poll), and 16 spinning warps issuing those starved the CTA's own loads (first
-  // version: 23 us per CG iteration).
+  // Spin with RELAXED gpu-scope loads and NO acquire fence.  ld.acquire.gpu / fence.acq_rel.gpu compile to
+  // (MEMBAR +) CCTL.IVALL — an invalidate-all of the SM's L1 — and 16 warps issuing one each per exchange cost
+  // ~19 us per CG iteration (measured: 83 iterations in 1555 us with either form; a 4-CTA grid was as slow as a
+  // 64-CTA one, i.e. the cost was inside the SM).  The fence is not needed here: every cross-CTA value read after
+  // the spin (partial sums, neighbours' vectors, x) is loaded with ld.global.cg / ld.relaxed.gpu, which are served
+  // by L2 — the point of coherence — and are issued only after the tag load has returned (control dependency on
+  // its value); the writer's st.release.gpu made its data visible at L2 before the tag.
   for (int c = lane; c < G; c += 32) {
     const unsigned *t = B.tags + par * P2_MAX_CTAS + c;
     unsigned v;
@@ -97,7 +101,6 @@ __device__ __forceinline__ void p2_wait(const Pcg2Bufs &B, unsigned seq, double 
     } while (v < seq);
   }
   __syncwarp();
-  asm volatile("fence.acq_rel.gpu;" ::: "memory");
   for (int c = lane; c < G; c += 32) {
     const double *p = B.part + ((size_t)par * P2_MAX_CTAS + c) * 2;
     sg += __ldcg(p);
@@ -267,6 +270,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
   bool converged = false;
   double gamma0 = 0.0, gamma_old = 1.0, alpha_old = 1.0, gamma_last = 0.0;
   if (ok) {
+    long long c0 = clock64(), c_pub = 0, c_wait = 0, c_mat = 0;
     for (int it = 0; it <= B.max_cg; it++) {
       seq++;
       const int par = seq & 1;
@@ -300,8 +304,10 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
       }
       if (lane == 0) { wred[warp][0] = acc_g; wred[warp][1] = acc_d; }
       p2_publish(B, seq, wred);
+      { const long long c = clock64(); c_pub += c - c0; c0 = c; }
       double gamma, delta;
       p2_wait(B, seq, gamma, delta);
+      { const long long c = clock64(); c_wait += c - c0; c0 = c; }
       gamma_last = gamma;
       if (it == 0) gamma0 = gamma;
       if (!(gamma == gamma) || !(delta == delta)) { ok = false; break; }
@@ -351,7 +357,9 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
         }
       }
       __syncwarp();
+      { const long long c = clock64(); c_mat += c - c0; c0 = c; }
     }
+    if (blockIdx.x == 0 && tid == 32) { state->prof[0] = c_pub; state->prof[1] = c_wait; state->prof[2] = c_mat; }
   }
 
   if (blockIdx.x == 0 && tid == 0) state->t[2] = gtimer();
