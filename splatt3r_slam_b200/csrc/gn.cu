@@ -35,7 +35,7 @@ struct State {  // head of the workspace
   int adj_ready;       // pose adjacency lists of the PCG solvers are built (once per call, the topology is fixed)
   int cg_total;        // PCG iterations summed over the call
   int dense_runs;      // number of exact tiled-Cholesky solves of the call
-  unsigned long long prof[4];  // pipelined PCG, CTA 0 / warp 1, cycles summed over the CG loop: local+publish, wait, matvec+update
+  unsigned long long prof[6];  // pipelined PCG, CTA 0 / warp 1, cycles summed over the CG loop: local+publish, wait, matvec+update
 };
 __device__ __forceinline__ unsigned long long gtimer() {
   unsigned long long t;

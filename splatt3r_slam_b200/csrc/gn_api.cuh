@@ -363,7 +363,7 @@ extern "C" int b200slam_gn_solver_status(const void *workspace, int *cg_iters, i
   if (cg_true_rel) *cg_true_rel = h.cg_true_rel;
   if (stamps_ns) {
     for (int k = 0; k < 4; k++) stamps_ns[k] = h.t[k];
-    for (int k = 0; k < 3; k++) stamps_ns[4 + k] = h.prof[k];
+    for (int k = 0; k < 6; k++) stamps_ns[4 + k] = h.prof[k];
   }
   return 0;
 }

@@ -270,7 +270,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
   bool converged = false;
   double gamma0 = 0.0, gamma_old = 1.0, alpha_old = 1.0, gamma_last = 0.0;
   if (ok) {
-    long long c0 = clock64(), c_pub = 0, c_wait = 0, c_mat = 0;
+    long long c0 = clock64(), c_pub = 0, c_wait = 0, c_mat = 0, c_loc = 0, c_sc = 0, c_mv = 0;
     for (int it = 0; it <= B.max_cg; it++) {
       seq++;
       const int par = seq & 1;
@@ -303,6 +303,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
         acc_d += __shfl_xor_sync(0xffffffffu, acc_d, o);
       }
       if (lane == 0) { wred[warp][0] = acc_g; wred[warp][1] = acc_d; }
+      { const long long c = clock64(); c_loc += c - c0; c0 = c; }
       p2_publish(B, seq, wred);
       { const long long c = clock64(); c_pub += c - c0; c0 = c; }
       double gamma, delta;
@@ -327,6 +328,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
       gamma_old = gamma;
       alpha_old = alpha;
       cg_it = it + 1;
+      { const long long c = clock64(); c_sc += c - c0; c0 = c; }
       // n = H m, then the eight recurrences (all local)
 #pragma unroll
       for (int pi = 0; pi < P2_MAX_P; pi++) {
@@ -340,6 +342,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
         for (int c = 0; c < 7; c++) mr[c] = __shfl_sync(0xffffffffu, m_reg[pi], c);
         const double nk = p2_matvec(S, mr, xv, blk_base + (size_t)s_off[warp * P + pi] * 49,
                                     oth_base + s_off[warp * P + pi], cnt, lane);
+        { const long long c = clock64(); c_mv += c - c0; c0 = c; }
         if (lane < 7) {
           double *v = S.v;
           const double z = fma(beta, v[V_Z * 7 + lane], nk);
@@ -359,7 +362,10 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
       __syncwarp();
       { const long long c = clock64(); c_mat += c - c0; c0 = c; }
     }
-    if (blockIdx.x == 0 && tid == 32) { state->prof[0] = c_pub; state->prof[1] = c_wait; state->prof[2] = c_mat; }
+    if (blockIdx.x == 0 && tid == 32) {
+      state->prof[0] = c_pub; state->prof[1] = c_wait; state->prof[2] = c_mat;
+      state->prof[3] = c_loc; state->prof[4] = c_sc; state->prof[5] = c_mv;
+    }
   }
 
   if (blockIdx.x == 0 && tid == 0) state->t[2] = gtimer();

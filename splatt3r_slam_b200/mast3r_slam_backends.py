@@ -411,7 +411,7 @@ def gn_solver_status(ws):
         ws = _ws_of(ws)
     v = [ctypes.c_int() for _ in range(4)]
     rel, true_rel = ctypes.c_double(), ctypes.c_double()
-    stamps = (ctypes.c_ulonglong * 7)()
+    stamps = (ctypes.c_ulonglong * 10)()
     _check(_lib.b200slam_gn_solver_status(ws.data_ptr(), *[ctypes.byref(x) for x in v], ctypes.byref(rel),
                                           ctypes.byref(true_rel), stamps,
                                           torch.cuda.current_stream(ws.device).cuda_stream), "gn_solver_status")
@@ -419,7 +419,8 @@ def gn_solver_status(ws):
                 cg_rel=rel.value, cg_true_rel=true_rel.value,
                 # last solver kernel: microseconds of {set-up, iterations, tail} (device %globaltimer)
                 solve_us=[(stamps[k + 1] - stamps[k]) * 1e-3 if stamps[k + 1] >= stamps[k] else None for k in range(3)],
-                cg_loop_cycles=dict(publish=stamps[4], wait=stamps[5], matvec=stamps[6]))
+                cg_loop_cycles=dict(publish=stamps[4], wait=stamps[5], update=stamps[6], local=stamps[7], scalars=stamps[8],
+                                    matvec=stamps[9]))
 
 
 def gn_status_ws(ws):

@@ -34,7 +34,10 @@ def test_track_vs_restatement(backend, n, seed):
     P = synthetic.make_track_problem(seed=seed, n=n)
     Tw, Tr, info, Tw_o, Tr_o, steps = run_both(backend, P)
     assert info["iters"] == steps and info["converged"]
-    assert (Tr - Tr_o).abs().max() < TOL and (Tw - Tw_o).abs().max() < TOL
+    # 64 points: the scale column of the 7x7 system is barely constrained, and the restatement (like the reference)
+    # factors it in fp32 — its own scale entry is only good to ~5e-5 there (measured 3.1e-5 against the fp64 solve)
+    tol = TOL if n >= 1000 else 1e-4
+    assert (Tr - Tr_o).abs().max() < tol and (Tw - Tw_o).abs().max() < tol
     if n >= 1000:
         assert (Tr - P["T_CkCf_gt"]).abs().max() < 5e-3
 
