@@ -35,7 +35,7 @@ constexpr int P2_WARPS = P2_THREADS / 32;
 constexpr int P2_MAX_CTAS = 160;
 constexpr int P2_MAX_P = 8;                            // poses per warp
 constexpr int P2_POSE_DOUBLES = 49 + 49 + 7 + 8 * 7;  // D, Dinv, b, 8 vectors
-constexpr int P2_SMEM_BYTES = 200 * 1024;              // dynamic shared memory opt-in
+constexpr int P2_SMEM_BYTES = 190 * 1024;              // dynamic shared memory opt-in (+ ~30 KB static <= 227 KB)
 
 struct Pcg2Bufs {
   const int *adj_ptr;   // (M+1)
@@ -81,68 +81,79 @@ __device__ __forceinline__ void p2_publish(const Pcg2Bufs &B, unsigned seq, doub
   __syncthreads();  // wred may be rewritten
 }
 
-// Wait until every CTA has published `seq`, then return the two grid sums (identical bits on every warp
-// of every CTA: lane c sums slots c, c+32, ... in order, then a fixed xor tree).
-__device__ __forceinline__ void p2_wait(const Pcg2Bufs &B, unsigned seq, double &g, double &d) {
+// Wait until every CTA has published `seq`, then return the two grid sums (identical bits on every CTA: lane c
+// sums slots c, c+32, ... in order, then a fixed xor tree).  ONE warp polls and the rest of the CTA waits at a
+// block barrier: tools/micro/xchg_latency.cu measures 2.4 k cycles per exchange at 64 CTAs this way against
+// 8.0 k with all 16 warps polling (their loads queue up in front of the tag stores at the L2 slice).
+// Polling uses RELAXED gpu-scope loads and NO acquire fence: ld.acquire.gpu / fence.acq_rel.gpu compile to
+// CCTL.IVALL (invalidate-all of the SM's L1), which is not needed here — every cross-CTA value read afterwards
+// (partial sums, neighbours' vectors, x) is loaded with ld.global.cg, i.e. from L2, the point of coherence, and
+// is issued only after the tag load has returned (control dependency); the writer's st.release.gpu made its data
+// visible at L2 before the tag.
+__device__ __forceinline__ void p2_wait(const Pcg2Bufs &B, unsigned seq, double &g, double &d, double *s_sum) {
   const int lane = threadIdx.x & 31, par = seq & 1, G = gridDim.x;
-  double sg = 0.0, sd = 0.0;
-  // Spin with RELAXED gpu-scope loads and NO acquire fence.  ld.acquire.gpu / fence.acq_rel.gpu compile to
-  // (MEMBAR +) CCTL.IVALL — an invalidate-all of the SM's L1 — and 16 warps issuing one each per exchange cost
-  // ~19 us per CG iteration (measured: 83 iterations in 1555 us with either form; a 4-CTA grid was as slow as a
-  // 64-CTA one, i.e. the cost was inside the SM).  The fence is not needed here: every cross-CTA value read after
-  // the spin (partial sums, neighbours' vectors, x) is loaded with ld.global.cg / ld.relaxed.gpu, which are served
-  // by L2 — the point of coherence — and are issued only after the tag load has returned (control dependency on
-  // its value); the writer's st.release.gpu made its data visible at L2 before the tag.
-  for (int c = lane; c < G; c += 32) {
-    const unsigned *t = B.tags + par * P2_MAX_CTAS + c;
-    unsigned v;
-    do {
-      asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(t) : "memory");
-    } while (v < seq);
-  }
-  __syncwarp();
-  for (int c = lane; c < G; c += 32) {
-    const double *p = B.part + ((size_t)par * P2_MAX_CTAS + c) * 2;
-    sg += __ldcg(p);
-    sd += __ldcg(p + 1);
-  }
+  if (threadIdx.x < 32) {
+    double sg = 0.0, sd = 0.0;
+    for (int c = lane; c < G; c += 32) {
+      const unsigned *t = B.tags + par * P2_MAX_CTAS + c;
+      unsigned v;
+      do {
+        asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(t) : "memory");
+      } while (v < seq);
+    }
+    __syncwarp();
+    for (int c = lane; c < G; c += 32) {
+      const double *p = B.part + ((size_t)par * P2_MAX_CTAS + c) * 2;
+      sg += __ldcg(p);
+      sd += __ldcg(p + 1);
+    }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    sg += __shfl_xor_sync(0xffffffffu, sg, o);
-    sd += __shfl_xor_sync(0xffffffffu, sd, o);
+    for (int o = 16; o > 0; o >>= 1) {
+      sg += __shfl_xor_sync(0xffffffffu, sg, o);
+      sd += __shfl_xor_sync(0xffffffffu, sd, o);
+    }
+    if (lane == 0) { s_sum[0] = sg; s_sum[1] = sd; }
   }
-  g = sg;
-  d = sd;
+  __syncthreads();
+  g = s_sum[0];
+  d = s_sum[1];
 }
 
-// (H v)_k of one pose for lane k < 7 (other lanes: garbage), v_r = own 7-vector, neighbours' vectors read
-// from the exchange buffer xv (L2).  28 lanes = 7 rows x 4 slices of the adjacency list; slices combined in
-// fixed order.
+// (H v)_k of one pose for lane k < 7 (other lanes: garbage), v_r = own 7-vector, neighbours' vectors read from the
+// exchange buffer xv (L2).  Two phases per chunk of up to 32 incident blocks: (1) the warp GATHERS the chunk's
+// neighbour entries (7 per block) into its shared-memory buffer nb, lane l taking entries l, l+32, ... — up to 7
+// independent L2 loads per lane in flight, ONE round trip (the first version had each lane load the 7 values of
+// its own blocks in sequence with the FMAs: 7 k cycles per pass); (2) 28 lanes = 7 rows x 4 slices of the chunk
+// multiply from shared memory; slices combined in fixed order.
+constexpr int P2_NB_BLOCKS = 32;
 __device__ __forceinline__ double p2_matvec(const P2Pose &S, const double *vr, const double *__restrict__ xv,
-                                            const double *blocks, const int *others, int cnt, int lane) {
+                                            const double *blocks, const int *others, int cnt, int lane, double *nb) {
   const int k = lane % 7, slice = lane / 7;
   double a = 0.0;
-  if (slice < 4) {
-    for (int t0 = slice; t0 < cnt; t0 += 16) {
-      double xo[4][7];
-      int o[4];
+  for (int base = 0; base < cnt; base += P2_NB_BLOCKS) {
+    const int m = min(P2_NB_BLOCKS, cnt - base), total = 7 * m;
+    double val[7];
 #pragma unroll
-      for (int u = 0; u < 4; u++) {  // issue all neighbour loads of up to 4 blocks before the FMAs
-        const int t = t0 + 4 * u;
-        o[u] = t < cnt ? others[t] : -1;
-#pragma unroll
-        for (int c = 0; c < 7; c++) xo[u][c] = o[u] >= 0 ? __ldcg(xv + (size_t)o[u] * 7 + c) : 0.0;
-      }
-#pragma unroll
-      for (int u = 0; u < 4; u++) {
-        const int t = t0 + 4 * u;
-        if (o[u] >= 0) {
-          const double *blk = blocks + (size_t)t * 49 + k * 7;
-#pragma unroll
-          for (int c = 0; c < 7; c++) a = fma(blk[c], xo[u][c], a);
-        }
+    for (int u = 0; u < 7; u++) {
+      const int idx = lane + 32 * u;
+      val[u] = 0.0;
+      if (idx < total) {
+        const int t = idx / 7, c = idx - 7 * t, o = others[base + t];
+        if (o >= 0) val[u] = __ldcg(xv + (size_t)o * 7 + c);
       }
     }
+#pragma unroll
+    for (int u = 0; u < 7; u++)
+      if (lane + 32 * u < total) nb[lane + 32 * u] = val[u];
+    __syncwarp();
+    if (slice < 4) {
+      for (int t = slice; t < m; t += 4) {
+        const double *blk = blocks + (size_t)(base + t) * 49 + k * 7;
+#pragma unroll
+        for (int c = 0; c < 7; c++) a = fma(blk[c], nb[t * 7 + c], a);
+      }
+    }
+    __syncwarp();
   }
   const double a1 = __shfl_sync(0xffffffffu, a, (lane + 7) & 31);
   const double a2 = __shfl_sync(0xffffffffu, a, (lane + 14) & 31);
@@ -165,6 +176,9 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
   __shared__ double fin_scratch[64];
   __shared__ int s_off[P2_WARPS * P2_MAX_P + 1];
   __shared__ int s_setup_fail;
+  __shared__ double s_sum[2];
+  __shared__ double s_nb[P2_WARPS][P2_NB_BLOCKS * 7];
+  double *nb = s_nb[threadIdx.x >> 5];
   const int M = N - NUM_FIX, D = 7 * M;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (blockIdx.x == 0 && tid == 0) state->t[0] = gtimer();
@@ -248,7 +262,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
   unsigned seq = 1;
   p2_publish(B, seq, wred);
   double gsum, dsum;
-  p2_wait(B, seq, gsum, dsum);
+  p2_wait(B, seq, gsum, dsum, s_sum);
   bool ok = gsum == 0.0;  // uniform over the grid
   if (blockIdx.x == 0 && tid == 0) state->t[1] = gtimer();
   // w0 = H u0
@@ -259,7 +273,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
       P2Pose S = p2_pose(pose_base, warp * P + pi);
       const int cnt = B.adj_ptr[pose + 1] - B.adj_ptr[pose];
       const double w = p2_matvec(S, S.v + V_U * 7, B.xch + (size_t)par0 * D, blk_base + (size_t)s_off[warp * P + pi] * 49,
-                                 oth_base + s_off[warp * P + pi], cnt, lane);
+                                 oth_base + s_off[warp * P + pi], cnt, lane, nb);
       if (lane < 7) S.v[V_W * 7 + lane] = w;
     }
     __syncwarp();
@@ -307,7 +321,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
       p2_publish(B, seq, wred);
       { const long long c = clock64(); c_pub += c - c0; c0 = c; }
       double gamma, delta;
-      p2_wait(B, seq, gamma, delta);
+      p2_wait(B, seq, gamma, delta, s_sum);
       { const long long c = clock64(); c_wait += c - c0; c0 = c; }
       gamma_last = gamma;
       if (it == 0) gamma0 = gamma;
@@ -341,7 +355,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
 #pragma unroll
         for (int c = 0; c < 7; c++) mr[c] = __shfl_sync(0xffffffffu, m_reg[pi], c);
         const double nk = p2_matvec(S, mr, xv, blk_base + (size_t)s_off[warp * P + pi] * 49,
-                                    oth_base + s_off[warp * P + pi], cnt, lane);
+                                    oth_base + s_off[warp * P + pi], cnt, lane, nb);
         { const long long c = clock64(); c_mv += c - c0; c0 = c; }
         if (lane < 7) {
           double *v = S.v;
@@ -385,7 +399,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
     if (lane == 0) { wred[warp][0] = 0.0; wred[warp][1] = 0.0; }
     p2_publish(B, seq, wred);
     double t0, t1;
-    p2_wait(B, seq, t0, t1);
+    p2_wait(B, seq, t0, t1, s_sum);
     acc_g = 0.0;
     if (ok && converged) {
       for (int pi = 0; pi < P; pi++) {
@@ -394,7 +408,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
         P2Pose S = p2_pose(pose_base, warp * P + pi);
         const int cnt = B.adj_ptr[pose + 1] - B.adj_ptr[pose];
         const double hx = p2_matvec(S, S.v + V_X * 7, xv, blk_base + (size_t)s_off[warp * P + pi] * 49,
-                                    oth_base + s_off[warp * P + pi], cnt, lane);
+                                    oth_base + s_off[warp * P + pi], cnt, lane, nb);
         const double rt = lane < 7 ? S.b[lane] - hx : 0.0;
         double rv[7];  // (r_true, Dinv r_true)
 #pragma unroll
@@ -413,7 +427,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
     seq++;
     p2_publish(B, seq, wred);
     double gamma_true;
-    p2_wait(B, seq, gamma_true, t1);
+    p2_wait(B, seq, gamma_true, t1, s_sum);
     const bool good = ok && converged && (gamma_true == gamma_true) && gamma_true <= B.true_tol2 * gamma0;
     if (blockIdx.x == 0) {
       if (tid == 0) {
