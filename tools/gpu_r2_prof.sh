@@ -22,4 +22,9 @@ echo "== solver1024"
 timeout 300 python tools/prof_r2.py solver1024 > $OUT/${TAG}_plain_s1024.log 2>&1 &&
 timeout 1500 $NCU -k regex:'pcg2_solve_retract_kernel' -s 1 -c 1 \
     -o $OUT/${TAG}_solver1024 -f python tools/prof_r2.py solver1024 > $OUT/${TAG}_ncu_s1024.log 2>&1; echo "rc=$?"
+# the reports are large (gpurun_out merges at most 64 MiB): export the raw counter pages here and drop the reports
+for R in tracker graph32 graph256 solver1024; do
+  [ -f $OUT/${TAG}_$R.ncu-rep ] && ncu -i $OUT/${TAG}_$R.ncu-rep --page raw --csv > $OUT/${TAG}_${R}_raw.csv 2>/dev/null
+  [ "$KEEP_REP" == "$R" ] || rm -f $OUT/${TAG}_$R.ncu-rep
+done
 ls -la $OUT | grep $TAG
