@@ -8,7 +8,7 @@
 //      and when the step is rejected the next iteration re-samples the unchanged pixel.  So ONE
 //      9-channel sample per iteration, at the proposed pixel, replaces both, and the dependent
 //      load rounds per iteration drop from two to one.
-//  (2) while the proposal stays inside the same integer pixel cell (the usual case after the
+//  (2) while the proposal stays inside the last sampled integer pixel cell (the usual case after the
 //      first few LM steps) the 36 raw taps are unchanged, so they are kept in registers and only
 //      re-weighted: no loads at all.
 #pragma once
@@ -46,18 +46,23 @@ __device__ __forceinline__ Resid residual(float c0, float c1, float c2, float p0
 
 // LM loop of one query: img = the 9 planes of its batch row, (u, v) = clamped start pixel (in/out),
 // (p0, p1, p2) = target ray.  Returns the converged flag.
+//
+// Register budget: ONE set of 36 raw taps, the taps of the LAST SAMPLED cell (tu, tv), whether or not that
+// proposal was accepted; the accepted state is only its 9 interpolated channels + residual.  (The first version
+// kept the accepted cell's taps AND the proposal's: 72 tap registers, 119 in total, 4 CTAs per SM.)  A proposal
+// in the sampled cell re-weights the registers, any other cell reloads — the same values either way, so the
+// result does not depend on the policy.
 __device__ __forceinline__ bool iter_proj_core(const float *__restrict__ img, int hw, int w, float umax, float vmax,
                                                float &u, float &v, float p0, float p1, float p2, int max_iter,
                                                float lambda_init, float cost_thresh) {
   float lambda = lambda_init;
   bool conv = false;
   if (max_iter > 0) {
-    // state at the current (accepted) pixel: taps of its cell, the 9 interpolated channels, residual
     float T[9][4], c[9];
-    int bu = (int)floorf(u), bv = (int)floorf(v);
-    load_taps<9>(T, img, hw, w, bu, bv);
+    int tu = (int)floorf(u), tv = (int)floorf(v);
+    load_taps<9>(T, img, hw, w, tu, tv);
     {
-      const Weights k = bilinear_weights(__fsub_rn(u, (float)bu), __fsub_rn(v, (float)bv));
+      const Weights k = bilinear_weights(__fsub_rn(u, (float)tu), __fsub_rn(v, (float)tv));
 #pragma unroll
       for (int j = 0; j < 9; j++) c[j] = tap(k, T[j][0], T[j][1], T[j][2], T[j][3]);
     }
@@ -79,30 +84,20 @@ __device__ __forceinline__ bool iter_proj_core(const float *__restrict__ img, in
 
       const int u2 = (int)floorf(un), v2 = (int)floorf(vn);
       const Weights k2 = bilinear_weights(__fsub_rn(un, (float)u2), __fsub_rn(vn, (float)v2));
-      float Tn[9][4], cn[9];
-      if (u2 == bu && v2 == bv) {  // same cell: re-weight the taps already in registers
-#pragma unroll
-        for (int j = 0; j < 9; j++) {
-#pragma unroll
-          for (int t = 0; t < 4; t++) Tn[j][t] = T[j][t];
-        }
-      } else {
-        load_taps<9>(Tn, img, hw, w, u2, v2);
+      if (u2 != tu || v2 != tv) {  // another cell: reload (usually an L1 hit: neighbouring lanes sample neighbouring cells)
+        load_taps<9>(T, img, hw, w, u2, v2);
+        tu = u2;
+        tv = v2;
       }
+      float cn[9];
 #pragma unroll
-      for (int j = 0; j < 9; j++) cn[j] = tap(k2, Tn[j][0], Tn[j][1], Tn[j][2], Tn[j][3]);
+      for (int j = 0; j < 9; j++) cn[j] = tap(k2, T[j][0], T[j][1], T[j][2], T[j][3]);
       const Resid rn = residual(cn[0], cn[1], cn[2], p0, p1, p2);
       if (rn.cost < r.cost) {
         u = un;
         v = vn;
-        bu = u2;
-        bv = v2;
 #pragma unroll
-        for (int j = 0; j < 9; j++) {
-          c[j] = cn[j];
-#pragma unroll
-          for (int t = 0; t < 4; t++) T[j][t] = Tn[j][t];
-        }
+        for (int j = 0; j < 9; j++) c[j] = cn[j];
         r = rn;
         lambda = __double2float_rn(__dmul_rn((double)lambda, 0.1));  // matching_kernels.cu:261
         conv = rn.cost < cost_thresh;

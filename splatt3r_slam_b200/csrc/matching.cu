@@ -56,7 +56,7 @@ __device__ __forceinline__ float dot3(float a0, float a1, float a2, float b0, fl
 
 constexpr int IP_THREADS = 128;
 #ifndef IP_MIN_CTAS
-#define IP_MIN_CTAS 4  // resident CTAs per SM the LM kernels are compiled for (A/B: 4 = 119 registers, no spills)
+#define IP_MIN_CTAS 6  // resident CTAs per SM the LM kernels are compiled for (A/B r02: 4 = 96 registers, 6 = 80, 8 = 64 with 100 B of spills)
 #endif
 
 // Pre-pass: (h*w, 9) interleaved -> 9 planes of h*w floats (per batch row), through shared memory
