@@ -123,7 +123,10 @@ namespace b200gn {
 
 // ---- stage 1 ----------------------------------------------------------------------------------
 template <int KIND, bool FUSED>
-__global__ void __launch_bounds__(BUILD_THREADS, 2)
+#ifndef BUILD_MIN_CTAS
+#define BUILD_MIN_CTAS 2  // resident CTAs per SM the build kernel is compiled for (A/B r02: 3 = 80 registers)
+#endif
+__global__ void __launch_bounds__(BUILD_THREADS, BUILD_MIN_CTAS)
 build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__ Cs,
              const int64_t *__restrict__ ii_row, const int64_t *__restrict__ jj_row,
              const int64_t *__restrict__ idx, const uint8_t *__restrict__ valid,
