@@ -55,7 +55,7 @@ struct Layout {
 // 148 SMs.  S is chosen to fill whole waves of 296 (measured on B200, N=32/E=128: 384 CTAs =
 // 1.3 waves ran 27% slower than 256 CTAs), with at least 512 points per CTA.
 // B200SLAM_GN_SPLITS overrides S (tuning aid).
-constexpr int CTA_SLOTS = 296;
+constexpr int CTA_SLOTS = 444;  // 148 SMs x BUILD_MIN_CTAS (3) resident CTAs
 constexpr int MAX_SPLITS = 160;
 inline int choose_splits(int Ecount, int n) {
   static const int forced = getenv("B200SLAM_GN_SPLITS") ? atoi(getenv("B200SLAM_GN_SPLITS")) : 0;
@@ -124,7 +124,7 @@ namespace b200gn {
 // ---- stage 1 ----------------------------------------------------------------------------------
 template <int KIND, bool FUSED>
 #ifndef BUILD_MIN_CTAS
-#define BUILD_MIN_CTAS 2  // resident CTAs per SM the build kernel is compiled for (A/B r02: 3 = 80 registers)
+#define BUILD_MIN_CTAS 3  // resident CTAs per SM the build kernel is compiled for: 80 registers, 24 warps/SM (A/B r02q at N=256: 2 CTAs = 117 registers 3.99 ms, 3 CTAs 3.46 ms, 4 CTAs = 64 registers + spills 3.81 ms)
 #endif
 __global__ void __launch_bounds__(BUILD_THREADS, BUILD_MIN_CTAS)
 build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__ Cs,
