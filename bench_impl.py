@@ -294,7 +294,7 @@ def graph_block(N, E, kind, rank, world, dev, steps, warmup, compare_1gpu=True):
     iterations per step with delta_thresh = 0.  Returns the result dict on rank 0 (None elsewhere).
     Phase times come from a separate pass with events around each phase (max over ranks)."""
     from splatt3r_slam_b200 import synthetic
-    from splatt3r_slam_b200.dist_gn import CudaHooks, EdgeBlockGather, gauss_newton_sharded, shard_range
+    from splatt3r_slam_b200.dist_gn import CudaHooks, EdgeBlockGather, EdgeBlockPush, gauss_newton_sharded, shard_range
     import splatt3r_slam_b200.mast3r_slam_backends as be
     n, iters = N_PIX, GN["iters"]
     e0, Ec = shard_range(E, rank, world)
@@ -315,11 +315,14 @@ def graph_block(N, E, kind, rank, world, dev, steps, warmup, compare_1gpu=True):
     def reset(h):
         be._check(be._lib.b200slam_gn_reset(h.ws.data_ptr(), h.nbytes, h._stream()), "gn_reset")
 
+    use_push = EdgeBlockPush.available(dev) and not os.environ.get("B200SLAM_NO_P2P")
+    push = EdgeBlockPush(E, rank, world, dev) if use_push else False
+
     def step():
         T = g["Twc"].clone()
         reset(hooks)
         gauss_newton_sharded(prm, T, g["Xs"], g["Cs"], K, g["ii"], g["jj"], idx_s, val_s, Q_s, iters, 0.0,
-                             hooks=hooks, rows=rows)
+                             hooks=hooks, rows=rows, push=push)
         return T
 
     for _ in range(max(2, warmup)):
@@ -344,11 +347,19 @@ def graph_block(N, E, kind, rank, world, dev, steps, warmup, compare_1gpu=True):
     _barrier(world)
     for it in range(iters):
         evs[it][0].record()
-        hooks.edge_blocks(Tp, g["Xs"], g["Cs"], K, rows[0], rows[1], idx_s, val_s, Q_s, e0, Ec, eb)
-        evs[it][1].record()
-        gather.run(eb)
+        if push:
+            seq = push.next_seq()
+            ebp = hooks.edge_blocks_push(Tp, g["Xs"], g["Cs"], K, rows[0], rows[1], idx_s, val_s, Q_s, e0, Ec, push, seq,
+                                         wait=False)
+            evs[it][1].record()
+            hooks.wait_peers(push, seq)
+        else:
+            hooks.edge_blocks(Tp, g["Xs"], g["Cs"], K, rows[0], rows[1], idx_s, val_s, Q_s, e0, Ec, eb)
+            evs[it][1].record()
+            gather.run(eb)
+            ebp = eb
         evs[it][2].record()
-        hooks.solve_retract(Tp, rows[0], rows[1], eb, 0.0, dx)
+        hooks.solve_retract(Tp, rows[0], rows[1], ebp, 0.0, dx)
         evs[it][3].record()
     _barrier(world)
     ph = [sum(e[k].elapsed_time(e[k + 1]) for e in evs) / iters for k in range(3)]
@@ -385,7 +396,11 @@ def graph_block(N, E, kind, rank, world, dev, steps, warmup, compare_1gpu=True):
         "workload": f"global_opt gauss_newton_{kind} N={N} keyframes E={E} directed edges 512x384, {iters} iters/step, "
                     f"edges sharded over {world} GPU(s) (strong scaling)",
         "iters_per_s": steps * iters / (ms * 1e-3), "ms_per_iter": per_iter_ms, "ms_per_step": ms / steps, "steps": steps,
-        "phase_ms_per_iter": {"build": ph[0], "allgather": ph[1], "solve": ph[2]},
+        # "exchange": with the fused push, the time the stream waits for the slowest peer's flag after its own
+        # build + peer stores (skew between ranks included); with NCCL, the all-gather call
+        "phase_ms_per_iter": {"build": ph[0], "exchange": ph[1], "solve": ph[2]},
+        "exchange": ("fused into the finalizing kernel: peer stores over NVLink symmetric memory + per-rank flags"
+                     if push else ("nccl all_gather_into_tensor" if world > 1 else "none (1 GPU)")),
         "solver": solver, "gn_status": st,
         "build_hbm": {"algorithmic_bytes_per_gpu": alg_bytes, "GBps": alg_bytes / (ph[0] * 1e-3) / 1e9,
                       "frac_of_peak": alg_bytes / (ph[0] * 1e-3) / 1e9 / peak, "peak": peak, "peak_source": peak_src},

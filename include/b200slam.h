@@ -132,6 +132,19 @@ int b200slam_gn_build_blocks(const b200slam_gn_params *prm, const float *Twc, co
  * edge_blocks (E,56) f64 = [H_jj (49, row-major) | g_j (7)] (H_ii = H_jj, H_ij = H_ji = -H_jj,
  * g_i = -g_j; gn_kernels.cu:998-999).  Rows outside the shard are left untouched, so a
  * zero-initialised buffer can be summed across ranks with one allreduce. */
+/* Multi-GPU (no counterpart in the reference, which is single-GPU): the same stage 1+2 with the exchange FUSED
+ * into the finalizing kernel — every edge block of the shard is stored straight into every rank's (E,56) array
+ * through peer pointers (host arrays peer_edge_blocks[world], peer_flags[world] of device pointers into NVLink-
+ * mapped symmetric memory), then flags[rank] = seq is released at system scope in every rank's flag array.
+ * b200slam_gn_wait_peers blocks the stream until all `world` flags of THIS rank's array have reached seq.
+ * Buffers must be double-buffered by the caller (ranks run at most one iteration apart). */
+int b200slam_gn_edge_blocks_push(const b200slam_gn_params *prm, const float *Twc, const float *Xs,
+                                 const float *Cs, const float *K, const int64_t *ii_row,
+                                 const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                                 const float *Q, int N, int E, int n, int e0, int Ecount,
+                                 double *const *peer_edge_blocks, unsigned *const *peer_flags, int world,
+                                 int rank, unsigned seq, void *workspace, size_t workspace_bytes, void *stream);
+int b200slam_gn_wait_peers(const unsigned *flags, int world, unsigned seq, void *stream);
 int b200slam_gn_edge_blocks(const b200slam_gn_params *prm, const float *Twc, const float *Xs,
                             const float *Cs, const float *K, const int64_t *ii_row,
                             const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,

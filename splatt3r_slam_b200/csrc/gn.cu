@@ -266,6 +266,67 @@ finalize_kernel(const float *__restrict__ Twc, const int64_t *__restrict__ ii_ro
   finalize_edge(Twc, ii_row, partials, S, e, wid, edge_blocks + (size_t)e * 56, sc[threadIdx.x >> 5], lane);
 }
 
+// ---- stage 2 fused with the exchange of the edge-sharded multi-GPU solve ------------------------
+// One warp per edge finalizes its block and stores the 56 doubles into EVERY rank's edge-block array through
+// NVLink peer pointers (symmetric memory), so the "all-gather" is the kernel's own epilogue: no separate
+// collective, no staging copy.  The last CTA of the launch (ticket) then publishes flags[rank] = seq in every
+// rank's flag array with a system-scope release; consumers wait with peers_wait_kernel.  The buffers are
+// double-buffered by the caller (a rank can run at most one iteration ahead of its peers).
+constexpr int MAX_PEERS = 16;
+struct PeerPtrs {
+  double *blocks[MAX_PEERS];    // each rank's (E,56) edge-block array
+  unsigned *flags[MAX_PEERS];   // each rank's flag array (>= world entries)
+};
+__global__ void __launch_bounds__(128)
+finalize_push_kernel(const float *__restrict__ Twc, const int64_t *__restrict__ ii_row,
+                     const double *__restrict__ partials, int S, int e0, int Ecount, PeerPtrs P, int world, int rank,
+                     unsigned seq, State *state) {
+  const int wid = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
+  __shared__ double sc[4][FIN_SCRATCH];
+  __shared__ bool is_last;
+  if (!state->done && wid < Ecount) {
+    const int e = e0 + wid;
+    double *own = P.blocks[rank] + (size_t)e * 56;
+    finalize_edge(Twc, ii_row, partials, S, e, wid, own, sc[threadIdx.x >> 5], lane);
+    const double v0 = own[lane], v1 = lane + 32 < 56 ? own[lane + 32] : 0.0;  // written by this warp (syncwarp inside)
+    for (int p = 0; p < world; p++) {
+      if (p == rank) continue;
+      double *dst = P.blocks[p] + (size_t)e * 56;
+      dst[lane] = v0;
+      if (lane + 32 < 56) dst[lane + 32] = v1;
+    }
+  }
+  // completion: every CTA's peer stores happen-before its ticket increment; the last CTA's system-scope release
+  // fence is cumulative over them
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    cuda::atomic_ref<unsigned, cuda::thread_scope_device> ticket(state->ticket);
+    is_last = ticket.fetch_add(1u, cuda::memory_order_acq_rel) == gridDim.x - 1;
+  }
+  __syncthreads();
+  if (is_last) {
+    if (threadIdx.x == 0) state->ticket = 0;
+    if ((int)threadIdx.x < world) {
+      __threadfence_system();
+      asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(P.flags[threadIdx.x] + rank), "r"(seq) : "memory");
+    }
+  }
+}
+
+// Wait until every rank has published `seq` (its rows of the edge-block array are in THIS rank's memory).
+__global__ void peers_wait_kernel(const unsigned *flags, int world, unsigned seq) {
+  const int p = threadIdx.x;
+  if (p < world) {
+    unsigned v;
+    do {
+      asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(flags + p) : "memory");
+    } while ((int)(v - seq) < 0);
+  }
+  __syncwarp();
+  asm volatile("fence.acq_rel.sys;" ::: "memory");
+}
+
 // reference-layout export: Hs (4,E,7,7) f32, gs (2,E,7) f32 (gn_kernels.cu:1119-1132)
 __global__ void export_blocks_kernel(const double *__restrict__ edge_blocks, int E, int e0, int Ecount,
                                      float *__restrict__ Hs, float *__restrict__ gs) {

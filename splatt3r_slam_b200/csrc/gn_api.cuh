@@ -388,6 +388,48 @@ extern "C" int b200slam_gn_edge_blocks(const b200slam_gn_params *prm, const floa
                             edge_blocks, (char *)workspace, L, st);
 }
 
+extern "C" int b200slam_gn_edge_blocks_push(const b200slam_gn_params *prm, const float *Twc, const float *Xs,
+                                            const float *Cs, const float *K, const int64_t *ii_row,
+                                            const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,
+                                            const float *Q, int N, int E, int n, int e0, int Ecount,
+                                            double *const *peer_edge_blocks, unsigned *const *peer_flags, int world,
+                                            int rank, unsigned seq, void *workspace, size_t workspace_bytes,
+                                            void *stream) {
+  if (bad_args(prm, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, N, E, n, workspace) || !peer_edge_blocks ||
+      !peer_flags || e0 < 0 || Ecount < 0 || e0 + Ecount > E || world < 1 || world > MAX_PEERS || rank < 0 ||
+      rank >= world)
+    return B200SLAM_EINVAL;
+  const Layout L = make_layout(N, E, n);
+  if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
+  cudaStream_t st = (cudaStream_t)stream;
+  int rc = check_K(prm, K);
+  if (rc) return rc;
+  BuildConsts C = make_consts(prm, K);
+  set_alignment(C, Xs, Cs, idx, valid, Q, n);
+  PeerPtrs P;
+  for (int p = 0; p < world; p++) {
+    if (!peer_edge_blocks[p] || !peer_flags[p]) return B200SLAM_EINVAL;
+    P.blocks[p] = peer_edge_blocks[p];
+    P.flags[p] = peer_flags[p];
+  }
+  char *ws = (char *)workspace;
+  State *state = reinterpret_cast<State *>(ws);
+  double *partials = reinterpret_cast<double *>(ws + L.partials);
+  const int S = splits_for(E, Ecount, n);
+  rc = launch_build(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, n, e0, Ecount, S, partials, state, st);
+  if (rc) return rc;
+  // even an empty shard publishes its flag (one CTA)
+  const int warps_per_cta = 4, ctas = Ecount > 0 ? (Ecount + warps_per_cta - 1) / warps_per_cta : 1;
+  finalize_push_kernel<<<ctas, 32 * warps_per_cta, 0, st>>>(Twc, ii_row, partials, S, e0, Ecount, P, world, rank, seq, state);
+  return (int)cudaGetLastError();
+}
+
+extern "C" int b200slam_gn_wait_peers(const unsigned *flags, int world, unsigned seq, void *stream) {
+  if (!flags || world < 1 || world > MAX_PEERS) return B200SLAM_EINVAL;
+  peers_wait_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(flags, world, seq);
+  return (int)cudaGetLastError();
+}
+
 extern "C" int b200slam_gn_build_blocks(const b200slam_gn_params *prm, const float *Twc, const float *Xs,
                                         const float *Cs, const float *K, const int64_t *ii_row,
                                         const int64_t *jj_row, const int64_t *idx, const uint8_t *valid,

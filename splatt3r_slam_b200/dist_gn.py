@@ -5,7 +5,10 @@ directed edges split into contiguous ranges, poses/pointmaps replicated.
 Per iteration, on every rank:
   1. stage 1+2 on the rank's own edges -> rows [e0, e0+Ec) of `edge_blocks` (E,56) fp64
      (= [H_jj | g_j] per edge, all other rows zero)                     [b200slam_gn_edge_blocks]
-  2. ONE collective: all-gather of the ranks' row ranges of `edge_blocks` over NCCL/NVLink (rows are
+  2. the exchange.  On NVLink-connected GPUs it is FUSED into step 1: the finalizing kernel stores each block into
+     every rank's array through peer pointers (symmetric memory) and releases a per-rank flag; the stream then
+     waits for all flags (EdgeBlockPush: no collective call at all).  Otherwise (gloo / CPU tests, no symmetric
+     memory) ONE collective: all-gather of the ranks' row ranges of `edge_blocks` over NCCL/NVLink (rows are
      disjoint, so nothing is summed: every rank ends with bit-identical blocks and the replicated
      solve below stays in lock-step).  Equal shards use all_gather_into_tensor in place; ragged
      shards (E % world != 0) a padded one.
@@ -53,6 +56,24 @@ class CudaHooks:
             vp(valid_s, 1), vp(Q_s, 4), self.N, self.E, n, e0, Ec, out.data_ptr(), self.ws.data_ptr(),
             self.nbytes, self._stream()), "gn_edge_blocks")
 
+    def edge_blocks_push(self, Twc, Xs, Cs, K, ii_row, jj_row, idx_s, valid_s, Q_s, e0, Ec, push, seq, wait=True):
+        """Stage 1+2 with the exchange fused into the finalizing kernel (`push`: an EdgeBlockPush)."""
+        n = self.n
+        vp = lambda t, esz: ctypes.c_void_p(t.data_ptr() - e0 * n * esz)
+        par = seq & 1
+        self.be._check(self.lib.b200slam_gn_edge_blocks_push(
+            ctypes.byref(self.prm), Twc.data_ptr(), Xs.data_ptr(), Cs.data_ptr(),
+            K.data_ptr() if K is not None else None, ii_row.data_ptr(), jj_row.data_ptr(), vp(idx_s, 8),
+            vp(valid_s, 1), vp(Q_s, 4), self.N, self.E, n, e0, Ec, push.block_ptrs[par], push.flag_ptrs, push.world,
+            push.rank, seq, self.ws.data_ptr(), self.nbytes, self._stream()), "gn_edge_blocks_push")
+        if wait:
+            self.wait_peers(push, seq)
+        return push.blocks[par]
+
+    def wait_peers(self, push, seq):
+        self.be._check(self.lib.b200slam_gn_wait_peers(push.flags.data_ptr(), push.world, seq, self._stream()),
+                       "gn_wait_peers")
+
     def solve_retract(self, Twc, ii_row, jj_row, edge_blocks, delta_thresh, dx):
         self.be._check(self.lib.b200slam_gn_solve_retract(
             Twc.data_ptr(), ii_row.data_ptr(), jj_row.data_ptr(), edge_blocks.data_ptr(), self.N, self.E,
@@ -92,9 +113,49 @@ class EdgeBlockGather:
                 edge_blocks[s0:s0 + sc].copy_(self.pad[r, :sc])
 
 
+class EdgeBlockPush:
+    """The exchange FUSED into the kernel that produces the blocks: two (E,56) fp64 edge-block arrays (ping-pong by
+    iteration parity) and a flag array per rank live in NVLink-mapped symmetric memory; `CudaHooks.edge_blocks_push`
+    has the finalizing kernel store every block of its shard into all ranks' arrays and release a per-rank sequence
+    flag, and makes the stream wait for all ranks' flags.  No NCCL call, no staging copy on the data path.
+    `available()` is False where symmetric memory cannot be set up (CPU / gloo tests, a single rank)."""
+    _seq = 0  # process-wide exchange counter: flags only ever increase, identical on all ranks (lock-step)
+
+    @staticmethod
+    def available(device):
+        if not (dist.is_initialized() and dist.get_world_size() > 1 and torch.device(device).type == "cuda"):
+            return False
+        try:
+            import torch.distributed._symmetric_memory  # noqa: F401
+            return dist.get_backend() == "nccl"
+        except Exception:  # noqa: BLE001
+            return False
+
+    def __init__(self, E, rank, world, device, group=None):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.E, self.rank, self.world = E, rank, world
+        name = (group or dist.group.WORLD).group_name
+        # one symmetric allocation: [blocks parity 0 | blocks parity 1 | flags (64 x u32, zero)]
+        nd = 2 * E * 56
+        self.buf = symm_mem.empty(nd + 32, dtype=torch.float64, device=device)
+        self.buf.zero_()
+        self.hdl = symm_mem.rendezvous(self.buf, name)
+        self.blocks = [self.buf[:E * 56].view(E, 56), self.buf[E * 56:nd].view(E, 56)]
+        self.flags = self.buf[nd:].view(torch.int32)
+        ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+        arr = ctypes.c_void_p * world
+        self.block_ptrs = [arr(*[p + par * E * 56 * 8 for p in ptrs]) for par in (0, 1)]
+        self.flag_ptrs = arr(*[p + nd * 8 for p in ptrs])
+        self.hdl.barrier()  # every rank's zeroed flags are in place before anyone pushes
+
+    def next_seq(self):
+        EdgeBlockPush._seq += 1
+        return EdgeBlockPush._seq
+
+
 def gauss_newton_sharded(prm, Twc, Xs, Cs, K, ii, jj, idx_shard, valid_shard, Q_shard, max_iter, delta_thresh,
-                         group=None, hooks=None, rows=None):
-    """Edge-sharded GN.  Twc (N,8) is updated in place on every rank (identically).
+                         group=None, hooks=None, rows=None, push=None):
+    """Edge-sharded GN.  `push`: an EdgeBlockPush to reuse (False: force the NCCL all-gather path).  Twc (N,8) is updated in place on every rank (identically).
     ii/jj: ALL E keyframe ids (replicated); idx/valid/Q: this rank's rows [e0, e0+Ec) of the
     (E,n,...) arrays, with (e0, Ec) = shard_range(E, rank, world).  Returns dx (N-1,7)."""
     world = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -110,6 +171,14 @@ def gauss_newton_sharded(prm, Twc, Xs, Cs, K, ii, jj, idx_shard, valid_shard, Q_
         hooks = CudaHooks(prm, N, E, n, Twc.device)
     edge_blocks = torch.zeros((E, 56), dtype=torch.float64, device=Twc.device)
     dx = torch.zeros((N - 1, 7), dtype=torch.float32, device=Twc.device)
+    if push is None and hasattr(hooks, "edge_blocks_push") and EdgeBlockPush.available(Twc.device):
+        push = EdgeBlockPush(E, rank, world, Twc.device, group)
+    if push:  # fused build + exchange over NVLink peer memory
+        for _ in range(max_iter):
+            eb = hooks.edge_blocks_push(Twc, Xs, Cs, K, ii_row, jj_row, idx_shard, valid_shard, Q_shard, e0, Ec, push,
+                                        push.next_seq())
+            hooks.solve_retract(Twc, ii_row, jj_row, eb, delta_thresh, dx)
+        return dx
     gather = EdgeBlockGather(E, rank, world, Twc.device, group)
     for _ in range(max_iter):
         hooks.edge_blocks(Twc, Xs, Cs, K, ii_row, jj_row, idx_shard, valid_shard, Q_shard, e0, Ec, edge_blocks)

@@ -44,6 +44,8 @@ def _load():
     lib.b200slam_gn_workspace_bytes.restype = sz
     lib.b200slam_gn_build_blocks.argtypes = [P] + [vp] * 9 + [i] * 5 + [vp, vp, vp, sz, vp]
     lib.b200slam_gn_edge_blocks.argtypes = [P] + [vp] * 9 + [i] * 5 + [vp, vp, sz, vp]
+    lib.b200slam_gn_edge_blocks_push.argtypes = [P] + [vp] * 9 + [i] * 5 + [vp, vp, i, i, ctypes.c_uint, vp, sz, vp]
+    lib.b200slam_gn_wait_peers.argtypes = [vp, i, ctypes.c_uint, vp]
     lib.b200slam_gn_solve_retract.argtypes = [vp] * 4 + [i, i, i, f, vp, vp, sz, vp]
     lib.b200slam_gn_reset.argtypes = [vp, sz, vp]
     lib.b200slam_gn_status.argtypes = [vp, ctypes.POINTER(i), ctypes.POINTER(i), ctypes.POINTER(i), vp]
@@ -64,7 +66,7 @@ def _load():
     lib.b200slam_match_workspace_bytes.restype = sz
     lib.b200slam_match.argtypes = [vp] * 4 + [i] + [vp] * 3 + [i] * 5 + [f, f, f, i, i, vp, sz, vp]
     for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "refine_matches_f64", "gn_build_blocks",
-                 "gn_edge_blocks", "gn_solve_retract", "gn_reset", "gn_status", "gn_solver_status", "gn_set_solver", "gauss_newton",
+                 "gn_edge_blocks", "gn_edge_blocks_push", "gn_wait_peers", "gn_solve_retract", "gn_reset", "gn_status", "gn_solver_status", "gn_set_solver", "gauss_newton",
                  "gauss_newton_ids", "gauss_newton_twoway", "edge_rows", "match", "track_ray_dist", "track_calib", "track_status"):
         getattr(lib, "b200slam_" + name).restype = i
     return lib
