@@ -126,7 +126,8 @@ class EdgeBlockPush:
         if not (dist.is_initialized() and dist.get_world_size() > 1 and torch.device(device).type == "cuda"):
             return False
         try:
-            import torch.distributed._symmetric_memory  # noqa: F401
+            import importlib
+            importlib.import_module("torch.distributed._symmetric_memory")
             return dist.get_backend() == "nccl"
         except Exception:  # noqa: BLE001
             return False
