@@ -174,9 +174,9 @@ int b200slam_gn_set_solver(int mode);
  * reference's counterpart is SparseBlock::solve's solver.info() (gn_kernels.cu:141-149), which it does not
  * expose.  cg_iters / cg_rel / cg_true_rel: iterations and relative (r, D^-1 r) — recursive and true — of
  * the last pipelined-PCG solve; cg_total: PCG iterations summed over the call; pcg_bad: the PCG gave up and
- * the exact tiled Cholesky took over; dense_runs: how many exact solves the call executed; stamps_ns[10]
+ * the exact tiled Cholesky took over; dense_runs: how many exact solves the call executed; stamps_ns[12]
  * (optional): %globaltimer at {start, set-up done, iterations done, end} of the last solver kernel, then its CG
- * loop's cycles in {publish, wait, recurrences, local dot products + D^-1 w, scalars, mat-vec} on one warp of CTA 0. */
+ * loop's cycles in {publish, wait, recurrences, local dot products + D^-1 w, scalars, mat-vec} on one warp of CTA 0, then the maximum and minimum over the CTAs of their non-waiting cycles. */
 int b200slam_gn_solver_status(const void *workspace, int *cg_iters, int *cg_total, int *pcg_bad,
                               int *dense_runs, double *cg_rel, double *cg_true_rel,
                               unsigned long long *stamps_ns, void *stream);

@@ -35,7 +35,8 @@ struct State {  // head of the workspace
   int adj_ready;       // pose adjacency lists of the PCG solvers are built (once per call, the topology is fixed)
   int cg_total;        // PCG iterations summed over the call
   int dense_runs;      // number of exact tiled-Cholesky solves of the call
-  unsigned long long prof[6];  // pipelined PCG, CTA 0 / warp 1, cycles summed over the CG loop: local+publish, wait, matvec+update
+  unsigned long long prof[6];
+  unsigned long long prof_busy_max, prof_busy_min;  // per-CTA non-waiting cycles of the CG loop: extrema over the grid  // pipelined PCG, CTA 0 / warp 1, cycles summed over the CG loop: local+publish, wait, matvec+update
 };
 __device__ __forceinline__ unsigned long long gtimer() {
   unsigned long long t;
@@ -43,6 +44,7 @@ __device__ __forceinline__ unsigned long long gtimer() {
   return t;
 }
 constexpr size_t STATE_BYTES = 256;
+static_assert(sizeof(State) <= STATE_BYTES, "State must fit the workspace head");
 
 __host__ __device__ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 

@@ -150,6 +150,10 @@ inline int launch_pcg2(float *Twc, const int64_t *ii_row, const int64_t *jj_row,
   B.true_tol2 = 1e-20;  // the same for the true residual of the returned x: 1e-10 in norm
   int rc = (int)cudaMemsetAsync(B.tags, 0, (size_t)2 * P2_MAX_CTAS * sizeof(unsigned), st);
   if (rc) return rc;
+  rc = (int)cudaMemsetAsync(&state->prof_busy_max, 0, 8, st);
+  if (rc) return rc;
+  rc = (int)cudaMemsetAsync(&state->prof_busy_min, 0xff, 8, st);
+  if (rc) return rc;
   rc = launch_adjacency(ii_row, jj_row, E, M, A, state, st);
   if (rc) return rc;
   static b200dev::Once attr;
@@ -364,6 +368,8 @@ extern "C" int b200slam_gn_solver_status(const void *workspace, int *cg_iters, i
   if (stamps_ns) {
     for (int k = 0; k < 4; k++) stamps_ns[k] = h.t[k];
     for (int k = 0; k < 6; k++) stamps_ns[4 + k] = h.prof[k];
+    stamps_ns[10] = h.prof_busy_max;
+    stamps_ns[11] = h.prof_busy_min;
   }
   return 0;
 }

@@ -180,6 +180,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
   __shared__ double wred[P2_WARPS][2];
   __shared__ double fin_scratch[64];
   __shared__ int s_off[P2_WARPS * P2_MAX_P + 1];
+  __shared__ int s_cnt[P2_WARPS * P2_MAX_P];  // distinct free neighbours per pose after merging
   __shared__ int s_setup_fail;
   __shared__ double s_sum[2];
   __shared__ double s_nb[P2_WARPS][P2_NB_BLOCKS * 7];
@@ -222,6 +223,11 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
       double *blocks = blk_base + (size_t)s_off[warp * P + pi] * 49;
       int *others = oth_base + s_off[warp * P + pi];
       double a0 = 0.0, a1 = 0.0;  // entries lane and lane + 32 of [D (49) | b (7)]
+      // Incident blocks are MERGED per neighbour while they are staged: the graph lists every edge in both
+      // directions (global_opt.py:104-110) and may repeat edges, and all of a pose's blocks towards the same
+      // neighbour o multiply the same x_o — summing them (in edge order: deterministic) halves the shared-memory
+      // bytes and the DFMAs of every mat-vec.  Blocks towards the fixed pose only enter D_r.
+      int m = 0;  // distinct free neighbours so far (warp-uniform)
       for (int t = 0; t < cnt; t++) {
         const int code = B.adj_list[t0 + t], e = code >> 1;
         const double *blk = eb + (size_t)e * 56;
@@ -230,10 +236,25 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
         a0 += v0;
         if (lane + 32 < 49) a1 += v1;
         else if (lane + 32 < 56) a1 += (code & 1) ? v1 : -v1;  // g_i = -g_j
-        blocks[(size_t)t * 49 + lane] = v0;
-        if (lane + 32 < 49) blocks[(size_t)t * 49 + lane + 32] = v1;
-        if (lane == 0) others[t] = (int)((code & 1) ? ii_row[e] : jj_row[e]) - NUM_FIX;  // < 0: the fixed pose
+        const int o = (int)((code & 1) ? ii_row[e] : jj_row[e]) - NUM_FIX;  // < 0: the fixed pose
+        if (o < 0) continue;  // warp-uniform
+        int j = -1;
+        for (int s0 = 0; s0 < m && j < 0; s0 += 32) {
+          const unsigned hit = __ballot_sync(0xffffffffu, s0 + lane < m && others[s0 + lane] == o);
+          if (hit) j = s0 + __ffs(hit) - 1;
+        }
+        if (j < 0) {
+          j = m++;
+          blocks[(size_t)j * 49 + lane] = v0;
+          if (lane + 32 < 49) blocks[(size_t)j * 49 + lane + 32] = v1;
+          if (lane == 0) others[j] = o;
+        } else {
+          blocks[(size_t)j * 49 + lane] += v0;
+          if (lane + 32 < 49) blocks[(size_t)j * 49 + lane + 32] += v1;
+        }
+        __syncwarp();
       }
+      if (lane == 0) s_cnt[warp * P + pi] = m;
       S.D[lane] = a0;
       if (lane + 32 < 49) S.D[lane + 32] = a1;
       else if (lane + 32 < 56) S.b[lane + 32 - 49] = a1;
@@ -276,7 +297,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
       const int pose = wg + pi * nW;
       if (pose >= M) continue;
       P2Pose S = p2_pose(pose_base, warp * P + pi);
-      const int cnt = B.adj_ptr[pose + 1] - B.adj_ptr[pose];
+      const int cnt = s_cnt[warp * P + pi];
       const double w = p2_matvec(S, S.v + V_U * 7, B.xch + (size_t)par0 * D, blk_base + (size_t)s_off[warp * P + pi] * 49,
                                  oth_base + s_off[warp * P + pi], cnt, lane, nb);
       if (lane < 7) S.v[V_W * 7 + lane] = w;
@@ -356,7 +377,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
         const int pose = wg + pi * nW;
         if (pose >= M) continue;
         P2Pose S = p2_pose(pose_base, warp * P + pi);
-        const int cnt = B.adj_ptr[pose + 1] - B.adj_ptr[pose];
+        const int cnt = s_cnt[warp * P + pi];
         double mr[7];  // own m as a 7-vector
 #pragma unroll
         for (int c = 0; c < 7; c++) mr[c] = __shfl_sync(0xffffffffu, m_reg[pi], c);
@@ -381,6 +402,11 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
       }
       __syncwarp();
       { const long long c = clock64(); c_mat += c - c0; c0 = c; }
+    }
+    if (tid == 32) {  // extrema over the CTAs of the non-waiting cycles (skew between CTAs shows up as others' wait)
+      const unsigned long long busy = (unsigned long long)(c_pub + c_mat + c_loc + c_sc + c_mv);
+      atomicMax(&state->prof_busy_max, busy);
+      atomicMin(&state->prof_busy_min, busy);
     }
     if (blockIdx.x == 0 && tid == 32) {
       state->prof[0] = c_pub; state->prof[1] = c_wait; state->prof[2] = c_mat;
@@ -412,7 +438,7 @@ pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const 
         const int pose = wg + pi * nW;
         if (pose >= M) continue;
         P2Pose S = p2_pose(pose_base, warp * P + pi);
-        const int cnt = B.adj_ptr[pose + 1] - B.adj_ptr[pose];
+        const int cnt = s_cnt[warp * P + pi];
         const double hx = p2_matvec(S, S.v + V_X * 7, xv, blk_base + (size_t)s_off[warp * P + pi] * 49,
                                     oth_base + s_off[warp * P + pi], cnt, lane, nb);
         const double rt = lane < 7 ? S.b[lane] - hx : 0.0;

@@ -413,7 +413,7 @@ def gn_solver_status(ws):
         ws = _ws_of(ws)
     v = [ctypes.c_int() for _ in range(4)]
     rel, true_rel = ctypes.c_double(), ctypes.c_double()
-    stamps = (ctypes.c_ulonglong * 10)()
+    stamps = (ctypes.c_ulonglong * 12)()
     _check(_lib.b200slam_gn_solver_status(ws.data_ptr(), *[ctypes.byref(x) for x in v], ctypes.byref(rel),
                                           ctypes.byref(true_rel), stamps,
                                           torch.cuda.current_stream(ws.device).cuda_stream), "gn_solver_status")
@@ -422,7 +422,7 @@ def gn_solver_status(ws):
                 # last solver kernel: microseconds of {set-up, iterations, tail} (device %globaltimer)
                 solve_us=[(stamps[k + 1] - stamps[k]) * 1e-3 if stamps[k + 1] >= stamps[k] else None for k in range(3)],
                 cg_loop_cycles=dict(publish=stamps[4], wait=stamps[5], update=stamps[6], local=stamps[7], scalars=stamps[8],
-                                    matvec=stamps[9]))
+                                    matvec=stamps[9], busy_max_over_ctas=stamps[10], busy_min_over_ctas=stamps[11]))
 
 
 def gn_status_ws(ws):
