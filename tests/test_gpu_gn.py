@@ -112,7 +112,10 @@ def test_vs_oracle_and_reference(backend, ref_backend, name, N, Eu, h, w):
     if ref_backend is not None:
         Tr = G["Twc"].clone()
         run(ref_backend, name, Tr, G, h, w, 5, 0.0)
-        assert rel(Tb, Tr) < RTOL
+        # the reference build sums 384..12288 fp32 terms per edge in its own order: after 5 iterations ITS poses sit
+        # up to ~1e-5 from the (fp64-solved) oracle's on the largest graph, so the bar against it is the contract
+        # plus that distance (measured: ours-vs-reference 1.07e-5 where oracle-vs-reference is of the same size)
+        assert rel(Tb, Tr) < RTOL + rel(To.to(dev()), Tr)
 
 
 def test_early_exit_keeps_reference_iteration_count(backend, golden):
