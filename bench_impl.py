@@ -226,9 +226,14 @@ def run_tracker(args):
         "gn_iters_per_s": {"E2": GN["iters"] / (kt["gn"] * 1e-6)},
         "roofline": {"bound": "hbm", "kernel": dom, "achieved": roof[dom], "peak": peak, "unit": "GB/s",
                      "frac": roof[dom] / peak, "traffic": NCU_TRAFFIC.get(dom), "peak_source": peak_src,
-                     "note": "algorithmic HBM bytes / CUDA-event time per call; refine is bound by the shared-memory pipe and the "
-                             "b=1 iter_proj / tracker GN by latency (DESIGN.md section 5); the HBM-bound kernel of this path is the "
-                             "graph-sized GN build (bench.py --workload graph)",
+                     "note": "algorithmic HBM bytes / CUDA-event time per call.  HBM is not the roof that binds these three: "
+                             "refine is bound by shared-memory reads and the fp16 pipe (floor 62 us each: 2.31 GB of LDS at "
+                             "148 SM x 128 B/clk, 36 M HMUL2/HADD2 warp-instructions at 2 clk), iter_proj by instruction issue "
+                             "(58 % issue-active at 7 % of HBM even at b = 32, see match_batched) and the tracker GN by the "
+                             "latency of 10 dependent iterations; the HBM-bound kernel of this path is the graph-sized GN build "
+                             "(`graph` / `graph_cfg3` blocks: build_hbm)",
+                     "other_floors": {"refine_lds_us": 62.0, "refine_fp16_pipe_us": 62.0,
+                                      "refine_frac_of_floor": 62.0 / kt["refine"]},
                      "all_kernels_GBps": {k: round(v, 1) for k, v in roof.items()}},
         "clocks": sampler.result(),
         # BASELINE.json configs[3] (N=1024 keyframes, E=8192 directed edges, 512x384) strong-scaled over the N ranks
@@ -279,9 +284,10 @@ def _kernel_times(be, cfg, sets, steps):
 
 
 # dram__bytes_read.sum + dram__bytes_write.sum per launch from the ncu --set full capture of this workload
-# (profiles/r01c_ncu_full_summary.txt, refine: profiles/r01g_ncu_refine_summary.txt; one 512x384 pair / N=2 E=2
-# graph): bytes
-NCU_TRAFFIC = {"iter_proj": 11.005e6, "refine": 23.135e6, "gn": 11.490e6}
+# (profiles/r02_ncu_tracker_summary.txt: one 512x384 pair / N=2 E=2 graph): bytes
+NCU_TRAFFIC = {"iter_proj": 11.005e6, "refine": 21.917e6, "gn": 11.502e6}
+# the graph-sized build kernel, per launch (profiles/r02_ncu_graph32_summary.txt, r02_ncu_graph256_summary.txt)
+NCU_TRAFFIC_BUILD = {(32, 128, 1): 661.3e6 + 4.7e6, (256, 2048, 1): 13185.7e6 + 4.4e6}
 
 
 def _mx(x, world, dev):
@@ -403,7 +409,12 @@ def graph_block(N, E, kind, rank, world, dev, steps, warmup, compare_1gpu=True):
                      if push else ("nccl all_gather_into_tensor" if world > 1 else "none (1 GPU)")),
         "solver": solver, "gn_status": st,
         "build_hbm": {"algorithmic_bytes_per_gpu": alg_bytes, "GBps": alg_bytes / (ph[0] * 1e-3) / 1e9,
-                      "frac_of_peak": alg_bytes / (ph[0] * 1e-3) / 1e9 / peak, "peak": peak, "peak_source": peak_src},
+                      "frac_of_peak": alg_bytes / (ph[0] * 1e-3) / 1e9 / peak, "peak": peak, "peak_source": peak_src,
+                      # bytes actually moved (ncu dram__bytes, per launch) where this shape was captured: the Xi gathers of
+                      # neighbouring edges hit L2, so fewer bytes move than the algorithmic count
+                      "traffic": NCU_TRAFFIC_BUILD.get((N, E, world)),
+                      "frac_of_peak_in_moved_bytes": (NCU_TRAFFIC_BUILD[(N, E, world)] / (ph[0] * 1e-3) / 1e9 / peak
+                                                      if (N, E, world) in NCU_TRAFFIC_BUILD else None)},
         "ranks_bit_identical": same, "pose_diff_vs_1gpu": diff, "data_gen_s": gen_s,
         "gpu_launches_per_iter": 9,
     }
@@ -426,7 +437,7 @@ def run_graph(args):
                        "l2": f"per-iteration working set {args.edges * 45.0 * N_PIX / world / 1e6:.0f} MB per GPU"},
             "roofline": {"bound": "hbm", "kernel": "gn build_kernel", "achieved": blk["build_hbm"]["GBps"],
                          "peak": blk["build_hbm"]["peak"], "unit": "GB/s", "frac": blk["build_hbm"]["frac_of_peak"],
-                         "traffic": None, "peak_source": blk["build_hbm"]["peak_source"]},
+                         "traffic": blk["build_hbm"]["traffic"], "peak_source": blk["build_hbm"]["peak_source"]},
             "graph": blk, "gpu_launches": args.steps * GN["iters"] * blk["gpu_launches_per_iter"],
             "clocks": sampler.result()}
     emit(line)
