@@ -9,7 +9,7 @@ TEST INFRASTRUCTURE ONLY.  Nothing in the product path imports this.
   vendored eigen) is compiled from the sources where they lie, unmodified, for sm_100a ->
   `oracle/_ref/lietorch_backends.so`.  `lietorch_extras` (:30-44) is not needed by any caller on the path.
 * The Python files (lietorch's 4 modules; splatt3r_slam's matching / image / geometry / nonlinear_optimizer /
-  tracker / global_opt / config / lietorch_utils) are compiled with `py_compile` to sourceless `.pyc` files under
+  tracker / global_opt / config / lietorch_utils) are compiled with `py_compile` to sourceless byte-code files (`.refbc`) under
   `oracle/_ref/refpy/` — binaries of the reference, like the `.so`: no reference SOURCE is copied into the
   repository, and `oracle/_ref/` is git-ignored (it travels to the GPU box, where /root/reference does not exist).
   `tests/refdrivers.py` imports them with stub modules for what the drivers import but the path never touches
@@ -61,7 +61,9 @@ def compile_python():
         for nm in names:
             if pkg == "splatt3r_slam" and nm == "__init__.py":
                 continue
-            cfile = os.path.join(d, nm[:-3] + ".pyc")
+            # ".refbc", not ".pyc": the GPU-box snapshot drops *.pyc files; tests/refdrivers.py loads these with
+            # importlib's SourcelessFileLoader, which does not care about the extension
+            cfile = os.path.join(d, nm[:-3] + ".refbc")
             # dfile: the path recorded in tracebacks — the reference file itself
             py_compile.compile(os.path.join(srcdir, nm), cfile=cfile, dfile=os.path.join(srcdir, nm), doraise=True)
             made.append(cfile)

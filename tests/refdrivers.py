@@ -13,6 +13,8 @@ The drivers are executed UNCHANGED; only what they import but the hot path never
 `config` is filled with the values of the reference's config/base.yaml (cited per block).
 """
 import importlib
+import importlib.abc
+import importlib.machinery
 import importlib.util
 import os
 import sys
@@ -42,7 +44,7 @@ BASE_CFG = {
 
 def available():
     return (os.path.exists(os.path.join(REF_DIR, "lietorch_backends.so"))
-            and os.path.exists(os.path.join(REFPY, "splatt3r_slam", "tracker.pyc")))
+            and os.path.exists(os.path.join(REFPY, "splatt3r_slam", "tracker.refbc")))
 
 
 class KeyframeStore:
@@ -73,6 +75,29 @@ class KeyframeStore:
         self.T_WC[idx] = T_WCs.data
 
 
+class _ByteCodeFinder(importlib.abc.MetaPathFinder):
+    """Resolves `lietorch[.x]` and `splatt3r_slam.x` to the sourceless byte-code files under oracle/_ref/refpy."""
+
+    def find_spec(self, fullname, path=None, target=None):
+        parts = fullname.split(".")
+        if parts[0] not in ("lietorch", "splatt3r_slam") or len(parts) > 2:
+            return None
+        pkg_dir = os.path.join(REFPY, parts[0])
+        if len(parts) == 1:
+            init = os.path.join(pkg_dir, "__init__.refbc")
+            if os.path.exists(init):
+                loader = importlib.machinery.SourcelessFileLoader(fullname, init)
+                return importlib.util.spec_from_file_location(fullname, init, loader=loader,
+                                                              submodule_search_locations=[pkg_dir])
+            spec = importlib.machinery.ModuleSpec(fullname, None, is_package=True)  # namespace package
+            spec.submodule_search_locations = [pkg_dir]
+            return spec
+        f = os.path.join(pkg_dir, parts[1] + ".refbc")
+        if not os.path.exists(f):
+            return None
+        return importlib.util.spec_from_file_location(fullname, f, loader=importlib.machinery.SourcelessFileLoader(fullname, f))
+
+
 _loaded = None
 
 
@@ -88,8 +113,8 @@ def load():
         mod = importlib.util.module_from_spec(spec)
         spec.loader.exec_module(mod)
         sys.modules["lietorch_backends"] = mod
-    if REFPY not in sys.path:
-        sys.path.insert(0, REFPY)
+    if not any(isinstance(f, _ByteCodeFinder) for f in sys.meta_path):
+        sys.meta_path.insert(0, _ByteCodeFinder())
     importlib.invalidate_caches()
     utils = types.ModuleType("splatt3r_slam.splatt3r_utils")
 
