@@ -20,8 +20,8 @@
 //     compute bit-identical alpha/beta and leave the loop together;
 //   * buffers are double-buffered by sequence parity (a CTA can run at most one exchange ahead).
 // Pipelined CG loses a few digits of attainable accuracy to its longer recurrences, so the kernel ends
-// with the TRUE residual b - H x (two more exchanges); unless that is below 1e-10 relative (and the
-// recursive one below 1e-12) within max_cg iterations, or if a curvature is not positive, it leaves the
+// with the TRUE residual b - H x (two more exchanges); unless that is below 1e-9 relative (and the
+// recursive one below 1e-10) within max_cg iterations, or if a curvature is not positive, it leaves the
 // poses alone and sets state->pcg_bad: the exact tiled Cholesky (gn_dense.cuh), enqueued right behind,
 // then runs instead of being skipped — for this and all later iterations of the call.  Ring-like graphs
 // (few loop closures: CG needs ~N iterations) therefore cost one capped PCG attempt per call.

@@ -205,7 +205,7 @@ def test_large_solve_matches_fp64_dense_solve(backend, N, Eu, h, w, solver):
         if (N, Eu) == (130, 130):
             assert st["pcg_bad"] == 1, st
         if (N, Eu) == (1024, 4096):
-            assert st["pcg_bad"] == 0 and 0 < st["cg_iters"] < 400 and st["cg_true_rel"] < 1e-20, st
+            assert st["pcg_bad"] == 0 and 0 < st["cg_iters"] < 400 and st["cg_true_rel"] < 1e-18, st
     ebc, ir, jr = eb.cpu(), ii_row.cpu() - 1, jj_row.cpu() - 1
     D = 7 * (N - 1)
     H = torch.zeros((D, D), dtype=torch.float64)
