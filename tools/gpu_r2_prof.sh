@@ -22,8 +22,11 @@ echo "== solver1024"
 timeout 300 python tools/prof_r2.py solver1024 > $OUT/${TAG}_plain_s1024.log 2>&1 &&
 timeout 1500 $NCU -k regex:'pcg2_solve_retract_kernel' -s 1 -c 1 \
     -o $OUT/${TAG}_solver1024 -f python tools/prof_r2.py solver1024 > $OUT/${TAG}_ncu_s1024.log 2>&1; echo "rc=$?"
+echo "== tcgen05 dense-correlation experiment"
+timeout 120 ./tools/micro/tc_corr > $OUT/${TAG}_tc_corr.txt 2>&1 &&
+timeout 600 $NCU -k regex:'corr_kernel' -s 2 -c 3 -o $OUT/${TAG}_tccorr -f ./tools/micro/tc_corr > $OUT/${TAG}_ncu_tccorr.log 2>&1; echo "rc=$?"
 # the reports are large (gpurun_out merges at most 64 MiB): export the raw counter pages here and drop the reports
-for R in tracker graph32 graph256 solver1024; do
+for R in tracker graph32 graph256 solver1024 tccorr; do
   [ -f $OUT/${TAG}_$R.ncu-rep ] && ncu -i $OUT/${TAG}_$R.ncu-rep --page raw --csv > $OUT/${TAG}_${R}_raw.csv 2>/dev/null
   [ "$KEEP_REP" == "$R" ] || rm -f $OUT/${TAG}_$R.ncu-rep
 done
