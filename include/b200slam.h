@@ -165,6 +165,20 @@ int b200slam_gn_solve_retract(float *Twc, const int64_t *ii_row, const int64_t *
 int b200slam_gn_reset(void *workspace, size_t workspace_bytes, void *stream);
 /* Read back {iterations executed, done flag, cholesky failures} (synchronises the stream). */
 int b200slam_gn_status(const void *workspace, int *iters, int *done, int *chol_fail, void *stream);
+/* Large graphs (7(N-1) > 217): decide, for THIS call, between the block-sparse Cholesky (graphs whose factor stays
+ * sparse under a minimum-degree ordering: odometry chains with few loop closures) and the pipelined PCG (graphs that
+ * fill in).  The analysis half of the reference's SimplicialLLT (ordering + symbolic factorisation,
+ * gn_kernels.cu:131-152, there re-done on the host every iteration) runs here once per topology: the 2E edge rows
+ * are copied to the host (ONE stream synchronisation), hashed, and only a changed topology is re-analysed; the plan
+ * lives in the workspace.  Call after b200slam_gn_reset and before the solves; b200slam_gauss_newton* do it
+ * themselves.  Without this call the PCG (with its exact dense fallback) is used. */
+int b200slam_gn_analyze(const int64_t *ii_row, const int64_t *jj_row, int N, int E, int n, void *workspace,
+                        size_t workspace_bytes, void *stream);
+/* The same plan executed on the HOST (no GPU): test aid that pins the ordering / symbolic factorisation / schedule.
+ * edge_blocks (E,56) and the rows are host pointers; x (7(N-1)) solves H x = b; returns 1 when H is not SPD.
+ * stats[4] = {off-diagonal blocks of L, block products, elimination-tree levels, 1 if within the device caps}. */
+int b200slam_gn_sparse_host_solve(const int64_t *ii_row, const int64_t *jj_row, const double *edge_blocks, int N, int E,
+                                  double *x, long long *stats);
 /* Large-graph (7(N-1) > 217) solver selection, process-wide: -1 = default (environment B200SLAM_GN_SOLVER,
  * else auto), 0 = auto (pipelined PCG, exact tiled Cholesky as gated fallback), 1 = exact tiled Cholesky
  * only, 2 = first-generation PCG.  A/B and test aid; all three solve the same system (the reference's
@@ -174,7 +188,8 @@ int b200slam_gn_set_solver(int mode);
  * reference's counterpart is SparseBlock::solve's solver.info() (gn_kernels.cu:141-149), which it does not
  * expose.  cg_iters / cg_rel / cg_true_rel: iterations and relative (r, D^-1 r) — recursive and true — of
  * the last pipelined-PCG solve; cg_total: PCG iterations summed over the call; pcg_bad: the PCG gave up and
- * the exact tiled Cholesky took over; dense_runs: how many exact solves the call executed; stamps_ns[12]
+ * the exact tiled Cholesky took over; dense_runs: low 16 bits = exact dense solves of the call, high bits =
+ * block-sparse Cholesky solves; stamps_ns[12]
  * (optional): %globaltimer at {start, set-up done, iterations done, end} of the last solver kernel, then its CG
  * loop's cycles in {publish, wait, recurrences, local dot products + D^-1 w, scalars, mat-vec} on one warp of CTA 0, then the maximum and minimum over the CTAs of their non-waiting cycles. */
 int b200slam_gn_solver_status(const void *workspace, int *cg_iters, int *cg_total, int *pcg_bad,

@@ -11,6 +11,9 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+#include <vector>
+
 #include "../../include/b200slam.h"
 #include "dev_cache.cuh"
 #include "gn_build.cuh"
@@ -36,7 +39,9 @@ struct State {  // head of the workspace
   int cg_total;        // PCG iterations summed over the call
   int dense_runs;      // number of exact tiled-Cholesky solves of the call
   unsigned long long prof[6];
-  unsigned long long prof_busy_max, prof_busy_min;  // per-CTA non-waiting cycles of the CG loop: extrema over the grid  // pipelined PCG, CTA 0 / warp 1, cycles summed over the CG loop: local+publish, wait, matvec+update
+  unsigned long long prof_busy_max, prof_busy_min;
+  int solver_sel;      // large graphs: 0 = pipelined PCG, 1 = block-sparse Cholesky (set by b200slam_gn_analyze for this call)
+  int sparse_runs;     // number of block-sparse Cholesky solves of the call  // per-CTA non-waiting cycles of the CG loop: extrema over the grid  // pipelined PCG, CTA 0 / warp 1, cycles summed over the CG loop: local+publish, wait, matvec+update
 };
 __device__ __forceinline__ unsigned long long gtimer() {
   unsigned long long t;
@@ -49,7 +54,8 @@ static_assert(sizeof(State) <= STATE_BYTES, "State must fit the workspace head")
 __host__ __device__ inline size_t align256(size_t x) { return (x + 255) & ~(size_t)255; }
 
 struct Layout {
-  size_t partials, edge_blocks, A, dense_ctrl, pcg, pcg2, rhs, rows, first, total;
+  size_t partials, edge_blocks, A, dense_ctrl, pcg, pcg2, sparse_ints, sparse_vals, rhs, rows, first, total;
+  int sparse_nl_cap, sparse_work_cap;
 };
 
 // Number of CTAs (S) that split the n points of one edge when `Ecount` edges are built by one
@@ -110,6 +116,18 @@ inline Layout make_layout(int N, int E, int n) {
   if (D > B200SLAM_SINGLE_CTA_MAX_D)
     off = align256(off + align256(2 * D * sizeof(double)) + align256((size_t)2 * 160 * 2 * sizeof(double)) +
                    align256((size_t)2 * 160 * sizeof(unsigned)));
+  // block-sparse Cholesky (gn_sparse.cuh): the plan's integer arrays and the value arrays, sized for the caps
+  // under which the sparse solver is chosen at all (b200slam_gn_analyze)
+  L.sparse_ints = L.sparse_vals = off;
+  L.sparse_nl_cap = L.sparse_work_cap = 0;
+  if (D > B200SLAM_SINGLE_CTA_MAX_D) {
+    const size_t Mp = D / 7;
+    L.sparse_nl_cap = (int)(48 * Mp < 65536 ? 48 * Mp : 65536);
+    L.sparse_work_cap = (int)(256 * Mp < 200000 ? 256 * Mp : 200000);
+    off = align256(off + (8 * Mp + 16 + 4 * (size_t)L.sparse_nl_cap + 3 * (size_t)L.sparse_work_cap + 5 * (size_t)E) * sizeof(int));
+    L.sparse_vals = off;
+    off = align256(off + (49 * Mp + 49 * (size_t)L.sparse_nl_cap + 28 * Mp) * sizeof(double));
+  }
   L.rhs = off; off = align256(off + D * sizeof(double));
   L.rows = off; off = align256(off + (size_t)2 * E * sizeof(int64_t));
   L.first = off; off = align256(off + (size_t)2 * E);
@@ -353,6 +371,8 @@ __global__ void export_blocks_kernel(const double *__restrict__ edge_blocks, int
 #include "gn_track.cuh"
 #include "gn_pcg.cuh"
 #include "gn_pcg2.cuh"
+#include "gn_sparse_plan.h"
+#include "gn_sparse.cuh"
 #include "gn_dense.cuh"
 #include "gn_api.cuh"
 #include "gn_track_api.cuh"

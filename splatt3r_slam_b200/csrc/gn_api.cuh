@@ -171,6 +171,70 @@ inline int launch_pcg2(float *Twc, const int64_t *ii_row, const int64_t *jj_row,
                                           (size_t)P2_SMEM_BYTES, st);
 }
 
+// ---- block-sparse Cholesky: host analysis (once per topology), plan upload, launch ------------------------------
+// Host-side record per workspace: which topology its uploaded plan belongs to.  The DEVICE decides per call
+// whether the plan is used (State::solver_sel, written by b200slam_gn_analyze after State was reset), so a stale
+// record can at worst launch one no-op kernel.
+struct SparseCacheEntry {
+  const void *ws = nullptr;
+  uint64_t hash = 0;
+  int N = 0, E = 0;
+  bool has_plan = false;
+  SparseDev dev{};
+};
+static SparseCacheEntry g_sparse_cache[8];
+static int g_sparse_cache_next = 0;
+static std::mutex g_sparse_mutex;
+
+inline SparseCacheEntry *sparse_lookup(const void *ws) {
+  for (auto &e : g_sparse_cache)
+    if (e.ws == ws) return &e;
+  return nullptr;
+}
+
+inline uint64_t hash_rows(const int64_t *a, const int64_t *b, int E, int N) {
+  uint64_t h = 1469598103934665603ull ^ (uint64_t)N;
+  auto mix = [&](uint64_t v) { h = (h ^ v) * 1099511628211ull; };
+  for (int e = 0; e < E; e++) { mix((uint64_t)a[e]); mix((uint64_t)b[e] + 0x9e3779b97f4a7c15ull); }
+  return h;
+}
+
+inline SparseDev sparse_dev_view(char *ws, const Layout &L, const b200sparse::Plan &P, int E) {
+  SparseDev d{};
+  d.M = P.M; d.nL = P.nL; d.levels = P.levels;
+  int *ip = reinterpret_cast<int *>(ws + L.sparse_ints);
+  auto take = [&](size_t n) { int *p = ip; ip += n; return p; };
+  d.perm = take(P.perm.size());
+  d.colptr = take(P.colptr.size());
+  d.rowidx = take(P.rowidx.size());
+  d.level_ptr = take(P.level_ptr.size());
+  d.level_cols = take(P.level_cols.size());
+  d.upd_ptr = take(P.upd_ptr.size());
+  d.upd = take(P.upd.size());
+  d.row_ptr = take(P.row_ptr.size());
+  d.row_ent = take(P.row_ent.size());
+  d.asm_ptr = take(P.asm_ptr.size());
+  d.asm_ent = take(P.asm_ent.size());
+  d.rhs_ptr = take(P.rhs_ptr.size());
+  d.rhs_ent = take(P.rhs_ent.size());
+  double *dp = reinterpret_cast<double *>(ws + L.sparse_vals);
+  d.Dg = dp; dp += (size_t)49 * P.M;
+  d.Lv = dp; dp += (size_t)49 * L.sparse_nl_cap;
+  d.y = dp; dp += (size_t)7 * P.M;
+  d.xs = dp; dp += (size_t)7 * P.M;
+  d.x = dp;
+  (void)E;
+  return d;
+}
+
+inline int launch_sparse(float *Twc, const double *edge_blocks, int N, float delta_thresh, float *dx, char *ws,
+                         const SparseCacheEntry &ce, cudaStream_t st) {
+  State *state = reinterpret_cast<State *>(ws);
+  SparseDev P = ce.dev;
+  sparse_solve_retract_kernel<<<1, SP_THREADS, 0, st>>>(Twc, edge_blocks, N, P, delta_thresh, dx, state);
+  return (int)cudaGetLastError();
+}
+
 // First-generation PCG (gn_pcg.cuh, solver mode "pcg1"): three counter barriers per CG iteration; kept as the
 // A/B baseline of the pipelined one.
 inline int launch_pcg(float *Twc, const int64_t *ii_row, const int64_t *jj_row, const double *edge_blocks, int N,
@@ -262,6 +326,14 @@ inline int launch_solve(float *Twc, const int64_t *ii_row, const int64_t *jj_row
     if (mode == 2) return launch_pcg(Twc, ii_row, jj_row, edge_blocks, N, E, delta_thresh, dx, ws, L, st);
     int gated = 0;
     if (mode == 0) {
+      {  // a plan uploaded for this workspace and graph size: the sparse kernel runs iff THIS call's analysis chose it
+        std::lock_guard<std::mutex> lock(g_sparse_mutex);
+        const SparseCacheEntry *ce = sparse_lookup(ws);
+        if (ce && ce->has_plan && ce->N == N && ce->E == E) {
+          const int rc = launch_sparse(Twc, edge_blocks, N, delta_thresh, dx, ws, *ce, st);
+          if (rc) return rc;
+        }
+      }
       const int rc = launch_pcg2(Twc, ii_row, jj_row, edge_blocks, N, E, delta_thresh, dx, ws, L, st);
       if (rc != 0 && rc != 1) return rc;
       gated = rc == 0;
@@ -348,6 +420,77 @@ extern "C" int b200slam_gn_status(const void *workspace, int *iters, int *done, 
   return 0;
 }
 
+// Large graphs only (7(N-1) > 217): choose between the block-sparse Cholesky and the PCG for THIS call.  Copies the
+// 2E edge rows to the host (synchronises the stream once), hashes them, re-runs the ordering + symbolic factorisation
+// only when the topology changed, uploads the plan into the workspace and writes State::solver_sel.  Must be
+// called after the State was reset for the call (b200slam_gn_reset / the drivers' own reset) and before the solves.
+extern "C" int b200slam_gn_analyze(const int64_t *ii_row, const int64_t *jj_row, int N, int E, int n, void *workspace,
+                                   size_t workspace_bytes, void *stream) {
+  if (!ii_row || !jj_row || !workspace || N < 2 || E < 0) return B200SLAM_EINVAL;
+  const Layout L = make_layout(N, E, n);
+  if (workspace_bytes < L.total) return B200SLAM_EWORKSPACE;
+  if (7 * (N - NUM_FIX) <= PACKED_MAX_D || L.sparse_nl_cap == 0) return 0;  // small graphs never get here
+  static const bool disabled = getenv("B200SLAM_GN_NO_SPARSE") != nullptr;
+  if (disabled || (g_solver_mode > 0)) return 0;
+  cudaStream_t st = (cudaStream_t)stream;
+  char *ws = (char *)workspace;
+  std::vector<int64_t> hi(E), hj(E);
+  cudaError_t err = cudaMemcpyAsync(hi.data(), ii_row, (size_t)E * 8, cudaMemcpyDeviceToHost, st);
+  if (err == cudaSuccess) err = cudaMemcpyAsync(hj.data(), jj_row, (size_t)E * 8, cudaMemcpyDeviceToHost, st);
+  if (err == cudaSuccess) err = cudaStreamSynchronize(st);
+  if (err != cudaSuccess) return (int)err;
+  const uint64_t h = hash_rows(hi.data(), hj.data(), E, N);
+  std::lock_guard<std::mutex> lock(g_sparse_mutex);
+  SparseCacheEntry *ce = sparse_lookup(ws);
+  if (!ce) {
+    ce = &g_sparse_cache[g_sparse_cache_next];
+    g_sparse_cache_next = (g_sparse_cache_next + 1) % 8;
+    *ce = SparseCacheEntry();
+    ce->ws = ws;
+  }
+  if (!(ce->hash == h && ce->N == N && ce->E == E)) {  // new topology for this workspace
+    ce->hash = h; ce->N = N; ce->E = E; ce->has_plan = false;
+    b200sparse::Plan P;
+    if (b200sparse::analyze(hi.data(), hj.data(), E, N, P, L.sparse_work_cap) && P.nL <= L.sparse_nl_cap) {
+      ce->dev = sparse_dev_view(ws, L, P, E);
+      const std::vector<int> *arrs[] = {&P.perm, &P.colptr, &P.rowidx, &P.level_ptr, &P.level_cols, &P.upd_ptr, &P.upd,
+                                        &P.row_ptr, &P.row_ent, &P.asm_ptr, &P.asm_ent, &P.rhs_ptr, &P.rhs_ent};
+      const int *dsts[] = {ce->dev.perm, ce->dev.colptr, ce->dev.rowidx, ce->dev.level_ptr, ce->dev.level_cols,
+                           ce->dev.upd_ptr, ce->dev.upd, ce->dev.row_ptr, ce->dev.row_ent, ce->dev.asm_ptr,
+                           ce->dev.asm_ent, ce->dev.rhs_ptr, ce->dev.rhs_ent};
+      for (int k = 0; k < 13; k++) {
+        if (arrs[k]->empty()) continue;
+        err = cudaMemcpyAsync(const_cast<int *>(dsts[k]), arrs[k]->data(), arrs[k]->size() * sizeof(int),
+                              cudaMemcpyHostToDevice, st);
+        if (err != cudaSuccess) return (int)err;
+      }
+      err = cudaStreamSynchronize(st);  // the host vectors die with this scope
+      if (err != cudaSuccess) return (int)err;
+      ce->has_plan = true;
+    }
+  }
+  State *state = reinterpret_cast<State *>(ws);
+  static const int one = 1, zero = 0;
+  err = cudaMemcpyAsync(&state->solver_sel, ce->has_plan ? &one : &zero, sizeof(int), cudaMemcpyHostToDevice, st);
+  return (int)err;
+}
+
+// Host execution of the same plan (no GPU involved): ordering + symbolic + numeric factorisation of the system the
+// edge blocks define, x (7(N-1)) in pose order.  Test aid: pins the plan the device kernel executes.
+// stats[0..3] = {off-diagonal blocks of L, block products, tree levels, 1 if the plan fits the device caps}.
+extern "C" int b200slam_gn_sparse_host_solve(const int64_t *ii_row, const int64_t *jj_row, const double *edge_blocks,
+                                             int N, int E, double *x, long long *stats) {
+  if (!ii_row || !jj_row || !edge_blocks || !x || N < 2 || E < 0) return B200SLAM_EINVAL;
+  b200sparse::Plan P;
+  if (!b200sparse::analyze(ii_row, jj_row, E, N, P, 1LL << 40)) return B200SLAM_EINVAL;
+  if (stats) {
+    const Layout L = make_layout(N, E, 0);
+    stats[0] = P.nL; stats[1] = P.work; stats[2] = P.levels;
+    stats[3] = (P.work <= L.sparse_work_cap && P.nL <= L.sparse_nl_cap) ? 1 : 0;
+  }
+  return b200sparse::solve_host(P, edge_blocks, x) ? 0 : 1;
+}
+
 extern "C" int b200slam_gn_set_solver(int mode) {
   if (mode < -1 || mode > 2) return B200SLAM_EINVAL;
   g_solver_mode = mode;
@@ -366,7 +509,7 @@ extern "C" int b200slam_gn_solver_status(const void *workspace, int *cg_iters, i
   if (cg_iters) *cg_iters = h.cg_iters;
   if (cg_total) *cg_total = h.cg_total;
   if (pcg_bad) *pcg_bad = h.pcg_bad;
-  if (dense_runs) *dense_runs = h.dense_runs;
+  if (dense_runs) *dense_runs = h.dense_runs + (h.sparse_runs << 16);  // low 16 bits: dense, high: block-sparse
   if (cg_rel) *cg_rel = h.cg_rel;
   if (cg_true_rel) *cg_true_rel = h.cg_true_rel;
   if (stamps_ns) {
@@ -494,6 +637,11 @@ inline int gauss_newton_run(const b200slam_gn_params *prm, const BuildConsts &C,
     rc = try_persistent(prm, C, Twc, Xs, Cs, ii_row, jj_row, idx, valid, Q, N, E, n, max_iter, delta_thresh, dx,
                         reinterpret_cast<double *>(ws + L.partials), eb, reinterpret_cast<State *>(ws), st);
     if (rc != 1) return rc;
+  }
+  if (7 * (N - NUM_FIX) > PACKED_MAX_D) {  // large graph: sparse direct solve or PCG? (one host sync per call)
+    const Layout &Lr = L;
+    rc = b200slam_gn_analyze(ii_row, jj_row, N, E, n, ws, Lr.total, st);
+    if (rc) return rc;
   }
   for (int it = 0; it < max_iter; it++) {
     if (fused) {  // one launch per iteration: the last stage-1 CTA runs stages 2-3

@@ -175,7 +175,8 @@ __global__ void __launch_bounds__(P2_THREADS, 1)
 pcg2_solve_retract_kernel(float *Twc, const int64_t *__restrict__ ii_row, const int64_t *__restrict__ jj_row,
                           const double *__restrict__ eb, int N, int E, int P, int blocks_cap, Pcg2Bufs B,
                           float delta_thresh, float *dx, State *state) {
-  if (state->done || state->pcg_bad) return;  // written only by earlier launches: uniform over the grid
+  // written only by earlier launches / copies on the stream: uniform over the grid
+  if (state->done || state->pcg_bad || state->solver_sel != 0) return;
   extern __shared__ __align__(16) double p2sm[];
   __shared__ double wred[P2_WARPS][2];
   __shared__ double fin_scratch[64];

@@ -74,6 +74,11 @@ class CudaHooks:
         self.be._check(self.lib.b200slam_gn_wait_peers(push.flags.data_ptr(), push.world, seq, self._stream()),
                        "gn_wait_peers")
 
+    def analyze(self, ii_row, jj_row):
+        """Large graphs: sparse direct solve or PCG for this call (one host sync; cached per topology)."""
+        self.be._check(self.lib.b200slam_gn_analyze(ii_row.data_ptr(), jj_row.data_ptr(), self.N, self.E, self.n,
+                                                    self.ws.data_ptr(), self.nbytes, self._stream()), "gn_analyze")
+
     def solve_retract(self, Twc, ii_row, jj_row, edge_blocks, delta_thresh, dx):
         self.be._check(self.lib.b200slam_gn_solve_retract(
             Twc.data_ptr(), ii_row.data_ptr(), jj_row.data_ptr(), edge_blocks.data_ptr(), self.N, self.E,
@@ -172,6 +177,8 @@ def gauss_newton_sharded(prm, Twc, Xs, Cs, K, ii, jj, idx_shard, valid_shard, Q_
         hooks = CudaHooks(prm, N, E, n, Twc.device)
     edge_blocks = torch.zeros((E, 56), dtype=torch.float64, device=Twc.device)
     dx = torch.zeros((N - 1, 7), dtype=torch.float32, device=Twc.device)
+    if hasattr(hooks, "analyze"):
+        hooks.analyze(ii_row, jj_row)
     if push is None and hasattr(hooks, "edge_blocks_push") and EdgeBlockPush.available(Twc.device):
         push = EdgeBlockPush(E, rank, world, Twc.device, group)
     if push:  # fused build + exchange over NVLink peer memory

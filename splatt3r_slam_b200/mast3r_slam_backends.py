@@ -52,6 +52,8 @@ def _load():
     D = ctypes.POINTER(ctypes.c_double)
     lib.b200slam_gn_solver_status.argtypes = [vp] + [ctypes.POINTER(i)] * 4 + [D, D, ctypes.POINTER(ctypes.c_ulonglong), vp]
     lib.b200slam_gn_set_solver.argtypes = [i]
+    lib.b200slam_gn_analyze.argtypes = [vp, vp, i, i, i, vp, sz, vp]
+    lib.b200slam_gn_sparse_host_solve.argtypes = [vp, vp, vp, i, i, vp, vp]
     lib.b200slam_gauss_newton.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_gauss_newton_ids.argtypes = [P] + [vp] * 9 + [i] * 4 + [f, vp, vp, sz, vp]
     lib.b200slam_edge_rows.argtypes = [vp, vp, i, vp, vp, sz, vp]
@@ -66,7 +68,7 @@ def _load():
     lib.b200slam_match_workspace_bytes.restype = sz
     lib.b200slam_match.argtypes = [vp] * 4 + [i] + [vp] * 3 + [i] * 5 + [f, f, f, i, i, vp, sz, vp]
     for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "refine_matches_f64", "gn_build_blocks",
-                 "gn_edge_blocks", "gn_edge_blocks_push", "gn_wait_peers", "gn_solve_retract", "gn_reset", "gn_status", "gn_solver_status", "gn_set_solver", "gauss_newton",
+                 "gn_edge_blocks", "gn_edge_blocks_push", "gn_wait_peers", "gn_solve_retract", "gn_reset", "gn_status", "gn_solver_status", "gn_set_solver", "gn_analyze", "gn_sparse_host_solve", "gauss_newton",
                  "gauss_newton_ids", "gauss_newton_twoway", "edge_rows", "match", "track_ray_dist", "track_calib", "track_status"):
         getattr(lib, "b200slam_" + name).restype = i
     return lib
@@ -179,7 +181,7 @@ def match(X11, X21, D11, D21, idx_1_to_2_init, max_iter, lambda_init, cost_thres
         idx = torch.empty((b, h * w), dtype=torch.int64, device=X11.device)
         valid = torch.empty((b, h * w, 1), dtype=torch.bool, device=X11.device)
         nbytes = _lib.b200slam_match_workspace_bytes(b, h, w, fdim, f32)
-        key = ("match", X11.device.index)
+        key = ("match", X11.device.index, _stream(X11))  # per (device, stream): two streams must not share scratch
         ws = _workspaces.get(key)
         if ws is None or ws.numel() < nbytes:
             ws = _workspaces[key] = torch.empty(max(int(nbytes), 16), dtype=torch.uint8, device=X11.device)
@@ -246,7 +248,7 @@ def track_calib(Xf, Xk, T_WCf, T_WCk, Qk, valid, meas_k, valid_meas_k, K, img_si
 
 def _track_workspace(device):
     nbytes = _lib.b200slam_track_workspace_bytes()
-    key = ("track", device.index)
+    key = ("track", device.index, torch.cuda.current_stream(device).cuda_stream)
     ws = _workspaces.get(key)
     if ws is None:
         ws = _workspaces[key] = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
@@ -286,11 +288,17 @@ _workspaces = {}
 
 
 def _workspace(device, nbytes):
-    key = (device.type, device.index)
+    """GN workspace, cached per (device, current stream): calls on different streams of one device must not share
+    the State / partials / ticket buffers (the reference allocates Hs/gs per call).  A workspace that has to grow
+    is replaced; the old tensor was only ever used on this same stream, so handing it back to the caching
+    allocator is ordered.  The last workspace used on a device is remembered for gn_status()."""
+    index = device.index if device.index is not None else torch.cuda.current_device()
+    key = (device.type, index, torch.cuda.current_stream(device).cuda_stream)
     ws = _workspaces.get(key)
     if ws is None or ws.numel() < nbytes:
         ws = torch.empty(int(nbytes), dtype=torch.uint8, device=device)
         _workspaces[key] = ws
+    _workspaces[(device.type, index)] = ws
     return ws
 
 
@@ -417,7 +425,8 @@ def gn_solver_status(ws):
     _check(_lib.b200slam_gn_solver_status(ws.data_ptr(), *[ctypes.byref(x) for x in v], ctypes.byref(rel),
                                           ctypes.byref(true_rel), stamps,
                                           torch.cuda.current_stream(ws.device).cuda_stream), "gn_solver_status")
-    return dict(cg_iters=v[0].value, cg_total=v[1].value, pcg_bad=v[2].value, dense_runs=v[3].value,
+    return dict(cg_iters=v[0].value, cg_total=v[1].value, pcg_bad=v[2].value, dense_runs=v[3].value & 0xffff,
+                sparse_runs=v[3].value >> 16,
                 cg_rel=rel.value, cg_true_rel=true_rel.value,
                 # last solver kernel: microseconds of {set-up, iterations, tail} (device %globaltimer)
                 solve_us=[(stamps[k + 1] - stamps[k]) * 1e-3 if stamps[k + 1] >= stamps[k] else None for k in range(3)],
