@@ -10,9 +10,10 @@
 // Shape: ONE CTA of 1024 threads.  The work is a few thousand 7x7 block products along an elimination tree of
 // 10-50 levels; what matters is the latency of a level, and a block barrier costs ~50 ns where a grid barrier
 // costs 1-2 us.  Phase 0 gathers all blocks of H from the edge blocks (one warp per block, fixed edge order);
-// then per tree level every warp takes columns: left-looking updates L_ij -= L_ik L_jk^T from the finished
-// descendant columns, 7x7 Cholesky of the diagonal block (its inverse W is kept), L_ij = A_ij W^T, and the
-// forward substitution of the column's right-hand side; the backward substitution walks the levels in reverse.
+// then per tree level: left-looking updates L_ij -= L_ik L_jk^T from the finished descendant columns, 7x7 Cholesky
+// of the diagonal block (its inverse W is kept), forward substitution of the column's right-hand side, and
+// L_ij = A_ij W^T — three block-synchronised phases so that levels with few, heavy columns still use all warps;
+// the backward substitution walks the levels in reverse.
 // All sums run in plan order => deterministic, bit-identical on every rank.
 #pragma once
 
@@ -99,31 +100,51 @@ sparse_solve_retract_kernel(float *Twc, const double *__restrict__ eb, int N, Sp
   __syncthreads();
   if (tid == 0) state->t[1] = gtimer();
   // ---- factorisation + forward substitution, level by level --------------------------------------------------
+  // Each level runs in three block-synchronised phases so that the levels near the root — few columns, each with
+  // hundreds of update triples and dozens of blocks — still use all 32 warps:
+  //   A  left-looking updates: g = 32 / (columns of the level) warps share a column; warp `sub` of the group takes
+  //      the triples whose DESTINATION block is congruent to sub mod g (no two warps touch one block, and every
+  //      block still receives its updates in plan order);
+  //   B  one warp per column: 7x7 Cholesky of the diagonal block (W = C^-1 kept), forward substitution;
+  //   C  L_ij = A_ij W^T, the column's blocks dealt to the same warp groups.
+  const int r0 = lane / 7, c0 = lane % 7, r1 = (lane + 32) / 7, c1 = (lane + 32) % 7;
   for (int l = 0; l < P.levels; l++) {
-    for (int c = P.level_ptr[l] + warp; c < P.level_ptr[l + 1]; c += SP_WARPS) {
+    const int lbeg = P.level_ptr[l], ncol = P.level_ptr[l + 1] - lbeg;
+    const int g = ncol >= SP_WARPS ? 1 : SP_WARPS / ncol;          // warps per column
+    const int stride = ncol >= SP_WARPS ? SP_WARPS : ncol;          // columns in flight per round
+    const int wcol = g == 1 ? warp : warp / g, sub = g == 1 ? 0 : warp % g;
+    // ---- A: updates ------------------------------------------------------------------------------------------
+    if (wcol < stride) {
+      for (int c = lbeg + wcol; c < lbeg + ncol; c += stride) {
+        const int j = P.level_cols[c];
+        double *D = P.Dg + (size_t)j * 49;
+        const int sbase = P.colptr[j];
+        for (int t = P.upd_ptr[j]; t < P.upd_ptr[j + 1]; t++) {
+          const int ds = P.upd[3 * t + 2];
+          if (g > 1 && ((ds < 0 ? 0 : 1 + ds - sbase) % g) != sub) continue;  // warp-uniform
+          const double *A = P.Lv + (size_t)P.upd[3 * t] * 49, *Bk = P.Lv + (size_t)P.upd[3 * t + 1] * 49;
+          double *dst = ds < 0 ? D : P.Lv + (size_t)ds * 49;
+          blkA[warp][lane] = A[lane];
+          blkB[warp][lane] = Bk[lane];
+          if (lane + 32 < 49) { blkA[warp][lane + 32] = A[lane + 32]; blkB[warp][lane + 32] = Bk[lane + 32]; }
+          __syncwarp();
+          double s0 = 0.0, s1 = 0.0;
+#pragma unroll
+          for (int q = 0; q < 7; q++) {
+            s0 = fma(blkA[warp][r0 * 7 + q], blkB[warp][c0 * 7 + q], s0);
+            if (lane + 32 < 49) s1 = fma(blkA[warp][r1 * 7 + q], blkB[warp][c1 * 7 + q], s1);
+          }
+          dst[lane] -= s0;
+          if (lane + 32 < 49) dst[lane + 32] -= s1;
+          __syncwarp();
+        }
+      }
+    }
+    __syncthreads();
+    // ---- B: diagonal block + forward substitution, one warp per column -------------------------------------
+    for (int c = lbeg + warp; c < lbeg + ncol; c += SP_WARPS) {
       const int j = P.level_cols[c];
       double *D = P.Dg + (size_t)j * 49;
-      // left-looking updates: dst -= L[a] L[b]^T, entries lane and lane + 32 of the 7x7 product
-      const int r0 = lane / 7, c0 = lane % 7, r1 = (lane + 32) / 7, c1 = (lane + 32) % 7;
-      for (int t = P.upd_ptr[j]; t < P.upd_ptr[j + 1]; t++) {
-        const double *A = P.Lv + (size_t)P.upd[3 * t] * 49, *Bk = P.Lv + (size_t)P.upd[3 * t + 1] * 49;
-        const int ds = P.upd[3 * t + 2];
-        double *dst = ds < 0 ? D : P.Lv + (size_t)ds * 49;
-        blkA[warp][lane] = A[lane];
-        blkB[warp][lane] = Bk[lane];
-        if (lane + 32 < 49) { blkA[warp][lane + 32] = A[lane + 32]; blkB[warp][lane + 32] = Bk[lane + 32]; }
-        __syncwarp();
-        double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-        for (int q = 0; q < 7; q++) {
-          s0 = fma(blkA[warp][r0 * 7 + q], blkB[warp][c0 * 7 + q], s0);
-          if (lane + 32 < 49) s1 = fma(blkA[warp][r1 * 7 + q], blkB[warp][c1 * 7 + q], s1);
-        }
-        dst[lane] -= s0;
-        if (lane + 32 < 49) dst[lane + 32] -= s1;
-        __syncwarp();
-      }
-      // diagonal block: Cholesky, W = C^-1 kept in D
       blkA[warp][lane] = D[lane];
       if (lane + 32 < 49) blkA[warp][lane + 32] = D[lane + 32];
       __syncwarp();
@@ -134,21 +155,7 @@ sparse_solve_retract_kernel(float *Twc, const double *__restrict__ eb, int N, Sp
       __syncwarp();
       D[lane] = blkA[warp][lane];
       if (lane + 32 < 49) D[lane + 32] = blkA[warp][lane + 32];
-      // column blocks: L_ij = A_ij W^T  (W lower triangular)
-      for (int s = P.colptr[j]; s < P.colptr[j + 1]; s++) {
-        double *Ls = P.Lv + (size_t)s * 49;
-        blkB[warp][lane] = Ls[lane];
-        if (lane + 32 < 49) blkB[warp][lane + 32] = Ls[lane + 32];
-        __syncwarp();
-        double v0 = 0.0, v1 = 0.0;
-        for (int q = 0; q <= c0; q++) v0 = fma(blkB[warp][r0 * 7 + q], blkA[warp][c0 * 7 + q], v0);
-        if (lane + 32 < 49)
-          for (int q = 0; q <= c1; q++) v1 = fma(blkB[warp][r1 * 7 + q], blkA[warp][c1 * 7 + q], v1);
-        Ls[lane] = v0;
-        if (lane + 32 < 49) Ls[lane + 32] = v1;
-        __syncwarp();
-      }
-      // forward substitution: y_j = W (b_j - sum_k L_jk y_k)
+      // forward substitution: y_j = W (b_j - sum_k L_jk y_k)   (row j's blocks belong to finished columns)
       double rhs = lane < 7 ? P.y[(size_t)j * 7 + lane] : 0.0;
       for (int t = P.row_ptr[j]; t < P.row_ptr[j + 1]; t++) {
         const int k = P.row_ent[2 * t];
@@ -169,6 +176,30 @@ sparse_solve_retract_kernel(float *Twc, const double *__restrict__ eb, int N, Sp
     }
     __syncthreads();
     if (s_fail) break;  // CTA-uniform after the barrier
+    // ---- C: column blocks L_ij = A_ij W^T (W lower triangular), dealt to the warp groups -------------------
+    if (wcol < stride) {
+      for (int c = lbeg + wcol; c < lbeg + ncol; c += stride) {
+        const int j = P.level_cols[c];
+        const double *Wj = P.Dg + (size_t)j * 49;
+        blkA[warp][lane] = Wj[lane];
+        if (lane + 32 < 49) blkA[warp][lane + 32] = Wj[lane + 32];
+        for (int s = P.colptr[j] + sub; s < P.colptr[j + 1]; s += g) {
+          double *Ls = P.Lv + (size_t)s * 49;
+          __syncwarp();
+          blkB[warp][lane] = Ls[lane];
+          if (lane + 32 < 49) blkB[warp][lane + 32] = Ls[lane + 32];
+          __syncwarp();
+          double v0 = 0.0, v1 = 0.0;
+          for (int q = 0; q <= c0; q++) v0 = fma(blkB[warp][r0 * 7 + q], blkA[warp][c0 * 7 + q], v0);
+          if (lane + 32 < 49)
+            for (int q = 0; q <= c1; q++) v1 = fma(blkB[warp][r1 * 7 + q], blkA[warp][c1 * 7 + q], v1);
+          Ls[lane] = v0;
+          if (lane + 32 < 49) Ls[lane + 32] = v1;
+        }
+        __syncwarp();
+      }
+    }
+    __syncthreads();
   }
   if (tid == 0) state->t[2] = gtimer();
   const bool ok = s_fail == 0;
