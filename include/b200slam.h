@@ -21,6 +21,7 @@ extern "C" {
 #define B200SLAM_OK 0
 #define B200SLAM_EINVAL (-1)    /* bad argument (null pointer, negative extent, n not supported) */
 #define B200SLAM_EWORKSPACE (-2) /* workspace too small */
+#define B200SLAM_ESTATIC_LIMIT (-3) /* input larger than the built-in scratch of an allocation-free entry point */
 
 /* Residual model of the Gauss-Newton build. */
 #define B200SLAM_GN_RAYS 0   /* ray + distance, gn_kernels.cu:812-1137 (ray_align_kernel)   */
@@ -40,6 +41,21 @@ int b200slam_iter_proj(const float *rays_img, const float *pts_3d_norm, const fl
                        float *p_new, uint8_t *converged, int b, int h, int w, int n, int max_iter,
                        float lambda_init, float cost_thresh, void *workspace, size_t workspace_bytes,
                        void *stream);
+
+/* Allocation-free variant of b200slam_iter_proj.  It has NO counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it): same inputs, outputs and bits as b200slam_iter_proj, but the planar
+ * copy of the ray image lives in a file-scope `static __device__` array of the library instead of a caller
+ * workspace, and the call performs no cudaMalloc / cudaFree / allocating library routine.
+ * Limit: b*h*w*9*4 bytes <= B200SLAM_ITER_PROJ_STATIC_MAX_BYTES (one 512x384 image, or any b*h*w <= 196 608);
+ * larger inputs return B200SLAM_ESTATIC_LIMIT and launch nothing.  Every GPU that loads the library holds the array
+ * until exit.  All calls on a device share it (nothing needs zeroing: each call overwrites what it reads), so calls
+ * that OVERLAP on the GPU - two streams - race; serialise them.  The first call on each device looks the array's
+ * address up (cudaGetSymbolAddress): make it before a graph capture starts. */
+#define B200SLAM_ITER_PROJ_STATIC_MAX_BYTES (196608 * 9 * 4)
+int b200slam_iter_proj_static(const float *rays_img, const float *pts_3d_norm, const float *p_init,
+                              float *p_new, uint8_t *converged, int b, int h, int w, int n, int max_iter,
+                              float lambda_init, float cost_thresh, void *stream);
 
 /* Replaces refine_matches_cuda / refine_matches_kernel<c10::Half>, matching_kernels.cu:24-115
  * (pybind gn.cpp:101-114).  D11 (b,h,w,fdim) f16; D21 (b,n,fdim) f16; p1 (b,n,2) i64 (u,v)

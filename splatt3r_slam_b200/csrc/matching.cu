@@ -111,6 +111,56 @@ extern "C" int b200slam_iter_proj(const float *rays_img, const float *pts_3d_nor
   return (int)cudaGetLastError();
 }
 
+// ---- allocation-free iter_proj (no counterpart in the reference) ----
+// For callers that cannot allocate (CUDA graph capture, tight serving loops): the planar copy of the ray image lives
+// in a file-scope device array instead of a caller-provided workspace.  Every GPU that loads the library holds these
+// B200SLAM_ITER_PROJ_STATIC_MAX_BYTES until exit.  Nothing in it has to start at zero (repack_planar_kernel
+// overwrites every word iter_proj_kernel reads), but ALL calls on a device share it: calls that overlap on the GPU
+// (different streams) race.
+__device__ __align__(256) float g_iter_proj_static_planes[B200SLAM_ITER_PROJ_STATIC_MAX_BYTES / sizeof(float)];
+
+namespace {
+// In host code the array's name is only a handle: the device address comes from cudaGetSymbolAddress, looked up once
+// per device with that device current.
+int iter_proj_static_planes(float **out) {
+  static float *addr[64] = {};
+  int d = 0;
+  cudaError_t err = cudaGetDevice(&d);
+  if (err != cudaSuccess) return (int)err;
+  if (d < 0 || d >= 64) return B200SLAM_EINVAL;
+  if (!addr[d]) {
+    void *p = nullptr;
+    err = cudaGetSymbolAddress(&p, g_iter_proj_static_planes);
+    if (err != cudaSuccess) return (int)err;
+    if (!p) return B200SLAM_EINVAL;
+    addr[d] = (float *)p;
+  }
+  *out = addr[d];
+  return B200SLAM_OK;
+}
+}  // namespace
+
+extern "C" int b200slam_iter_proj_static(const float *rays_img, const float *pts_3d_norm, const float *p_init,
+                                         float *p_new, uint8_t *converged, int b, int h, int w, int n,
+                                         int max_iter, float lambda_init, float cost_thresh, void *stream) {
+  if (b < 0 || n < 0) return B200SLAM_EINVAL;
+  if (b == 0 || n == 0) return B200SLAM_OK;
+  if (!rays_img || !pts_3d_norm || !p_init || !p_new || !converged) return B200SLAM_EINVAL;
+  if (h < 3 || w < 3 || (long long)h * w * 9 > 0x7fffffffLL) return B200SLAM_EINVAL;
+  if ((unsigned long long)b * h * w * 9ull * sizeof(float) > (unsigned long long)B200SLAM_ITER_PROJ_STATIC_MAX_BYTES)
+    return B200SLAM_ESTATIC_LIMIT;
+  float *planes = nullptr;
+  const int rc = iter_proj_static_planes(&planes);
+  if (rc != B200SLAM_OK) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  const int hw = h * w;
+  repack_planar_kernel<<<dim3((hw + IP_THREADS - 1) / IP_THREADS, b), IP_THREADS, 0, st>>>(rays_img, planes, hw);
+  dim3 grid((n + IP_THREADS - 1) / IP_THREADS, b);
+  iter_proj_kernel<<<grid, IP_THREADS, 0, st>>>(planes, pts_3d_norm, p_init, p_new, converged, h, w, n, max_iter,
+                                                lambda_init, cost_thresh);
+  return (int)cudaGetLastError();
+}
+
 // ---- fused match_iterative_proj --------------------------------------------
 extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, const int64_t *p1,
                                             int64_t *p1_new, int b, int h, int w, int n, int fdim,

@@ -35,6 +35,7 @@ def _load():
     P = ctypes.POINTER(GNParams)
     lib.b200slam_version.restype = i
     lib.b200slam_iter_proj.argtypes = [vp] * 5 + [i] * 5 + [f, f, vp, sz, vp]
+    lib.b200slam_iter_proj_static.argtypes = [vp] * 5 + [i] * 5 + [f, f, vp]
     lib.b200slam_iter_proj_workspace_bytes.argtypes = [i, i, i]
     lib.b200slam_iter_proj_workspace_bytes.restype = sz
     lib.b200slam_refine_matches_f16.argtypes = [vp] * 4 + [i] * 7 + [vp]
@@ -67,7 +68,7 @@ def _load():
     lib.b200slam_match_workspace_bytes.argtypes = [i] * 5
     lib.b200slam_match_workspace_bytes.restype = sz
     lib.b200slam_match.argtypes = [vp] * 4 + [i] + [vp] * 3 + [i] * 5 + [f, f, f, i, i, vp, sz, vp]
-    for name in ("iter_proj", "refine_matches_f16", "refine_matches_f32", "refine_matches_f64", "gn_build_blocks",
+    for name in ("iter_proj", "iter_proj_static", "refine_matches_f16", "refine_matches_f32", "refine_matches_f64", "gn_build_blocks",
                  "gn_edge_blocks", "gn_edge_blocks_push", "gn_wait_peers", "gn_solve_retract", "gn_reset", "gn_status", "gn_solver_status", "gn_set_solver", "gn_analyze", "gn_sparse_host_solve", "gauss_newton",
                  "gauss_newton_ids", "gauss_newton_twoway", "edge_rows", "match", "track_ray_dist", "track_calib", "track_status"):
         getattr(lib, "b200slam_" + name).restype = i
@@ -135,6 +136,34 @@ def iter_proj(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, co
             *ptrs, p_new.data_ptr(), conv.data_ptr(), b, h, w, n, int(max_iter), float(lambda_init),
             float(cost_thresh), ws.data_ptr(), nbytes, _stream(p_init)), "iter_proj")
     return [p_new, conv]
+
+
+ITER_PROJ_STATIC_MAX_BYTES = 196608 * 9 * 4  # B200SLAM_ITER_PROJ_STATIC_MAX_BYTES, include/b200slam.h
+
+
+def iter_proj_static(rays_img_with_grad, pts_3d_norm, p_init, max_iter, lambda_init, cost_thresh, p_new, converged):
+    """Allocation-free `iter_proj` (`b200slam_iter_proj_static`; no counterpart in the reference): the caller passes
+    the outputs `p_new` (b,n,2) f32 and `converged` (b,n) bool, the planar scratch is a static device array of the
+    library (at most ITER_PROJ_STATIC_MAX_BYTES = one 512x384 image).  Neither this wrapper nor the entry point
+    allocates; calls that overlap on the GPU share the scratch and race."""
+    _contig(rays_img_with_grad=rays_img_with_grad, pts_3d_norm=pts_3d_norm, p_init=p_init, p_new=p_new,
+            converged=converged)
+    b, h, w, c = rays_img_with_grad.shape
+    if c != 9:
+        raise RuntimeError("rays_img_with_grad must have 9 channels (ray, d/du, d/dv)")
+    n = p_init.shape[1]
+    if tuple(p_new.shape) != (b, n, 2) or tuple(converged.shape) != (b, n):
+        raise RuntimeError("iter_proj_static: p_new must be (b,n,2) and converged (b,n)")
+    if b * h * w * 36 > ITER_PROJ_STATIC_MAX_BYTES:
+        raise RuntimeError(f"iter_proj_static: b*h*w*36 = {b * h * w * 36} bytes of scratch exceed the built-in "
+                           f"{ITER_PROJ_STATIC_MAX_BYTES} (one 512x384 image); use iter_proj")
+    ptrs = (_cuda(rays_img_with_grad, torch.float32, "rays_img_with_grad"),
+            _cuda(pts_3d_norm, torch.float32, "pts_3d_norm"), _cuda(p_init, torch.float32, "p_init"),
+            _cuda(p_new, torch.float32, "p_new"), _cuda(converged, torch.bool, "converged"))
+    with _guard(p_init):
+        _check(_lib.b200slam_iter_proj_static(*ptrs, b, h, w, n, int(max_iter), float(lambda_init),
+                                              float(cost_thresh), _stream(p_init)), "iter_proj_static")
+    return [p_new, converged]
 
 
 def refine_matches(D11, D21, p1, radius, dilation_max):
