@@ -420,6 +420,16 @@ extern "C" int b200slam_gn_status(const void *workspace, int *iters, int *done, 
   return 0;
 }
 
+// Block products up to which the single-CTA block-sparse factorisation beats what runs otherwise when conjugate
+// gradients do not converge on a ring-like graph, the dense tiled Cholesky.  Measured on B200 (tools/sparse_probe.py,
+// profiles/r02c_sparse_probe.txt): sparse 0.39 us per block product (0.26 ms at 368 products ... 19.6 ms at 49 584),
+// dense 0.93 / 2.09 / 3.7 / 11.7 ms at N = 130 / 300 / 512 / 1024 = 5.8e-3 N + 5.3e-9 N^3 ms.
+inline long long sparse_work_limit(int N, long long layout_cap) {
+  const double dense_ms = 5.8e-3 * N + 5.3e-9 * (double)N * N * N;
+  const long long by_cost = (long long)(dense_ms / 0.39e-3);
+  return by_cost < layout_cap ? by_cost : layout_cap;
+}
+
 // Large graphs only (7(N-1) > 217): choose between the block-sparse Cholesky and the PCG for THIS call.  Copies the
 // 2E edge rows to the host (synchronises the stream once), hashes them, re-runs the ordering + symbolic factorisation
 // only when the topology changed, uploads the plan into the workspace and writes State::solver_sel.  Must be
@@ -451,7 +461,7 @@ extern "C" int b200slam_gn_analyze(const int64_t *ii_row, const int64_t *jj_row,
   if (!(ce->hash == h && ce->N == N && ce->E == E)) {  // new topology for this workspace
     ce->hash = h; ce->N = N; ce->E = E; ce->has_plan = false;
     b200sparse::Plan P;
-    if (b200sparse::analyze(hi.data(), hj.data(), E, N, P, L.sparse_work_cap) && P.nL <= L.sparse_nl_cap) {
+    if (b200sparse::analyze(hi.data(), hj.data(), E, N, P, sparse_work_limit(N, L.sparse_work_cap)) && P.nL <= L.sparse_nl_cap) {
       ce->dev = sparse_dev_view(ws, L, P, E);
       const std::vector<int> *arrs[] = {&P.perm, &P.colptr, &P.rowidx, &P.level_ptr, &P.level_cols, &P.upd_ptr, &P.upd,
                                         &P.row_ptr, &P.row_ent, &P.asm_ptr, &P.asm_ent, &P.rhs_ptr, &P.rhs_ent};
@@ -486,7 +496,7 @@ extern "C" int b200slam_gn_sparse_host_solve(const int64_t *ii_row, const int64_
   if (stats) {
     const Layout L = make_layout(N, E, 0);
     stats[0] = P.nL; stats[1] = P.work; stats[2] = P.levels;
-    stats[3] = (P.work <= L.sparse_work_cap && P.nL <= L.sparse_nl_cap) ? 1 : 0;
+    stats[3] = (P.work <= sparse_work_limit(N, L.sparse_work_cap) && P.nL <= L.sparse_nl_cap) ? 1 : 0;
   }
   return b200sparse::solve_host(P, edge_blocks, x) ? 0 : 1;
 }

@@ -186,7 +186,8 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
   // Tiled kernels with bulk-copy staged windows: queries form the (h, w) pixel grid of view 2
   // (n == h*w, as in matching.py:79-85), radius 3, and the nominal box of the coarsest level fits.
   const int reach = radius * dilation_max;
-  if (fdim == 24 && aligned && radius == 3 && n == h * w && dilation_max >= 1 && w >= rtile::TW + 2 * reach + 2) {
+  if (fdim == 24 && aligned && radius == 3 && n == h * w && dilation_max >= 1 && w >= rtile::TW + 2 * reach + 2 &&
+      (long long)h * w * 3 < 0x7fffffffLL) {
     // band count: fewest waves x rows-per-tile (time of a tile ~ its query rows); see refine_tile.cuh
     const int n_sm = b200dev::info().num_sms;
     const int tiles_x = (w + rtile::TW - 1) / rtile::TW, bands_min = (h + rtile::TH - 1) / rtile::TH;
@@ -205,7 +206,9 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
     const int tiles = tiles_x * bands;
     // a level whose full nominal box does not fit is scanned in two column passes of half the reach in x
     long long nominal = (long long)(rtile::TW + 2 * reach + rtile::SLACK) * (rtile::TH + 2 * reach + rtile::SLACK) * fdim * 2;
+#if !RT_LINEAR
     if (nominal > rtile::BOX_BYTES) nominal = (long long)(rtile::TW + reach + 2) * (rtile::TH + 2 * reach + 2) * fdim * 2;
+#endif
     if (nominal <= rtile::BOX_BYTES) {
       static b200dev::Once attr;  // function attributes are per device
       if (attr.first())
@@ -230,6 +233,16 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
                                                            dilation_max);
   return (int)cudaGetLastError();
 }
+
+#if RT_STATS
+// A/B builds only (-DRT_STATS=1): read and clear the per-level counters of the tiled kernel.
+extern "C" int b200slam_internal_refine_stats(unsigned long long *out32) {
+  cudaError_t err = cudaMemcpyFromSymbol(out32, rtile::g_rt_stats, sizeof(unsigned long long) * 32);
+  if (err != cudaSuccess) return (int)err;
+  static unsigned long long zeros[32] = {};
+  return (int)cudaMemcpyToSymbol(rtile::g_rt_stats, zeros, sizeof(zeros));
+}
+#endif
 
 extern "C" int b200slam_refine_matches_f16(const void *D11, const void *D21, const int64_t *p1,
                                            int64_t *p1_new, int b, int h, int w, int n, int fdim,

@@ -52,8 +52,23 @@ namespace rtile {
 #ifndef RT_PERMUTE_FIRST
 #define RT_PERMUTE_FIRST 1  // re-deal at the first (coarsest) level too (191.9 vs 193.4 us with the class-balanced deal)
 #endif
+#ifndef RT_LINEAR
+#define RT_LINEAR 0  // (measured: slower, see experiments/README.md) all candidates of a level as one scan-order list in groups of 8 (no odd seventh candidate per column; centre skipped after the first level)
+#endif
+#ifndef RT_PREFETCH
+#define RT_PREFETCH 0  // (measured: slower) software-pipelined candidate loads in scan_level
+#endif
+#ifndef RT_OVERFLOW_FIT
+#define RT_OVERFLOW_FIT 1  // a tile whose bounding box overflows stages the largest box that fits, not the nominal one
+#endif
 #ifndef RT_PERMUTE
 #define RT_PERMUTE 1  // re-deal the queries of a warp to its lanes per level so that quarter-warps hit distinct banks
+#endif
+#ifndef RT_STATS
+#define RT_STATS 0  // A/B builds only: per-level counters (live queries, queries outside the staged box, ...) in g_rt_stats
+#endif
+#if RT_STATS
+__device__ unsigned long long g_rt_stats[8][4];  // [dilation][live, out of box, tiles whose bounding box overflowed, tiles merged]
 #endif
 constexpr int TW = RT_TW, TH = RT_TH, THREADS = TW * TH, SLACK = RT_SLACK;
 constexpr int BOX_BYTES = RT_BOX_KB * 1024;  // shared-memory box per CTA
@@ -177,6 +192,78 @@ __device__ __forceinline__ void scan_column(const __half2 (&q)[FDIM / 2], int u,
   }
 }
 
+// All (2*RADIUS+1)^2 candidates of one level for one query as ONE list in the reference's scan order (u outer, v
+// inner, strict >), eight at a time = four HMUL2/HADD2 pairs with no idle half (a column of 7 leaves one).  The
+// centre candidate is scored at the first level only: at every later level the centre is the pixel whose score
+// IS max_score (the previous level's winner: same operands, same sum) or, when nothing has won yet, the
+// unchanged input pixel whose score already failed `> max_score` at the first level - it can never win again.  It
+// sits in the middle of the scan order (index 24 of 49), so the 48 others are exactly 3 + 3 groups around it.
+// roff / coff: element offsets (uint4 units) of the 7 clamped rows / columns; rmask / cmask: which lie in the image.
+// LOADER(offset, chunk) returns one 16-byte chunk.
+template <int FDIM, int RADIUS, class Loader>
+__device__ __forceinline__ void scan_level(const __half2 (&q)[FDIM / 2], const int (&roff)[2 * RADIUS + 1],
+                                           const int (&coff)[2 * RADIUS + 1], unsigned rmask, unsigned cmask,
+                                           bool with_centre, const Loader &load, float &max_score, int &best) {
+  constexpr int NJ = 2 * RADIUS + 1, NC = NJ * NJ, CT = RADIUS * NJ + RADIUS, G = 8, NG = (NC - 1) / G, NCH = FDIM / 8;
+  static_assert((NC - 1) % (2 * G) == 0, "the candidates before and after the centre must form whole groups");
+  // candidate number (scan order) of slot k of group g: the centre is not part of any group
+  auto cand = [](int g, int k) { return g * G + k < CT ? g * G + k : g * G + k + 1; };
+#if RT_PREFETCH
+  // software pipeline over the NG * NCH (group, chunk) steps: the eight 16-byte chunks of step s + 1 are requested
+  // before the 96 HMUL2/HADD2/PRMT of step s (ncu: short-scoreboard, i.e. waiting for LDS, was the top stall)
+  uint4 cb[2][G];
+#pragma unroll
+  for (int k = 0; k < G; k++) cb[0][k] = load(roff[cand(0, k) % NJ] + coff[cand(0, k) / NJ], 0);
+#endif
+  __half2 s2[G / 2];
+#pragma unroll
+  for (int g = 0; g < NG; g++) {
+    if (g == NG / 2 && with_centre) {
+      const int off = roff[RADIUS] + coff[RADIUS];
+      __half2 s1[1] = {__half2half2(__ushort_as_half(0))};
+#pragma unroll
+      for (int ch = 0; ch < NCH; ch++) {
+        const uint4 c[1] = {load(off, ch)};
+        const __half2 q4[4] = {q[ch * 4 + 0], q[ch * 4 + 1], q[ch * 4 + 2], q[ch * 4 + 3]};
+        mac_chunk_pairs<1>(s1, q4, c);
+      }
+      const float sf = __half2float(__low2half(s1[0]));
+      if (((rmask >> RADIUS) & (cmask >> RADIUS) & 1u) && sf > max_score) {
+        max_score = sf;
+        best = CT;
+      }
+    }
+#pragma unroll
+    for (int p = 0; p < G / 2; p++) s2[p] = __half2half2(__ushort_as_half(0));
+#pragma unroll
+    for (int ch = 0; ch < NCH; ch++) {
+      const __half2 q4[4] = {q[ch * 4 + 0], q[ch * 4 + 1], q[ch * 4 + 2], q[ch * 4 + 3]};
+#if RT_PREFETCH
+      const int s = g * NCH + ch, gn = (s + 1) / NCH, chn = (s + 1) % NCH;
+      if (s + 1 < NG * NCH) {
+#pragma unroll
+        for (int k = 0; k < G; k++) cb[(s + 1) & 1][k] = load(roff[cand(gn, k) % NJ] + coff[cand(gn, k) / NJ], chn);
+      }
+      mac_chunk_pairs<G>(s2, q4, cb[s & 1]);
+#else
+      uint4 c[G];
+#pragma unroll
+      for (int k = 0; k < G; k++) c[k] = load(roff[cand(g, k) % NJ] + coff[cand(g, k) / NJ], ch);
+      mac_chunk_pairs<G>(s2, q4, c);
+#endif
+    }
+#pragma unroll
+    for (int k = 0; k < G; k++) {
+      const int t = cand(g, k);
+      const float sf = __half2float((k & 1) ? __high2half(s2[k / 2]) : __low2half(s2[k / 2]));
+      if (((rmask >> (t % NJ)) & (cmask >> (t / NJ)) & 1u) && sf > max_score) {
+        max_score = sf;
+        best = t;
+      }
+    }
+  }
+}
+
 template <int FDIM, int RADIUS>
 __global__ void __launch_bounds__(THREADS, RT_BOX_KB > 113 ? 1 : 2)
 refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D21,
@@ -246,7 +333,11 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
     // A level whose nominal box (tile + reach + SLACK px) exceeds the shared-memory box is
     // scanned in two passes of candidate columns, i <= 0 then i > 0 (same i-outer scan order), each
     // with a box of half the reach in x.  With the default 224 KB box no level splits.
+#if RT_LINEAR
+    constexpr bool split = false;  // the host launches this build only when every level's nominal box fits
+#else
     const bool split = (TW + 2 * rd + SLACK) * (TH + 2 * rd + SLACK) > MAX_PX;
+#endif
     const int ilo = split && pass ? d : -rd, ihi = split && !pass ? 0 : rd;
     bool fresh = false;  // a copy was issued in this pass
     if (!merged) {
@@ -288,6 +379,9 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
         if (x1 >= x0 && y1 >= y0 && (x1 - x0 + 1) * (y1 - y0 + 1) <= MAX_PX) {
           b = Box{x0, y0, x1 - x0 + 1, y1 - y0 + 1};
           merged = true;
+#if RT_STATS
+          if (tid == 0) atomicAdd(&g_rt_stats[d & 7][3], 1ull);
+#endif
         }
       }
       if (c > 0 && !merged) {
@@ -295,8 +389,19 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
         int y0 = max(vmin - rd, 0), y1 = min(-nvmax + rd, h - 1);
         if (x1 >= x0 && y1 >= y0) {
           if ((x1 - x0 + 1) * (y1 - y0 + 1) > MAX_PX) {
+#if RT_STATS
+            if (tid == 0) atomicAdd(&g_rt_stats[d & 7][2], 1ull);
+#endif
+#if RT_OVERFLOW_FIT
+            // incoherent tile: the largest box of the bounding box's shape that fits, around the mean centre
+            const float shrink = sqrtf((float)MAX_PX / (float)((x1 - x0 + 1) * (y1 - y0 + 1)));
+            int side_x = max(min((int)((x1 - x0 + 1) * shrink), w), min(TW + ihi - ilo + 2, w));
+            int side_y = min(min(y1 - y0 + 1, h), MAX_PX / side_x);
+            side_x = min(min(x1 - x0 + 1, w), MAX_PX / side_y);
+#else
             // incoherent tile: keep a box of the nominal size around the mean centre
             const int side_x = min(TW + ihi - ilo + 2, w), side_y = min(min(TH + 2 * rd + 2, h), MAX_PX / side_x);
+#endif
             const int cx = su / c + (ilo + ihi) / 2, cy = sv / c;
             x0 = min(max(cx - side_x / 2, 0), w - side_x); x1 = x0 + side_x - 1;
             y0 = min(max(cy - side_y / 2, 0), h - side_y); y1 = y0 + side_y - 1;
@@ -387,6 +492,48 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
       // window clipped to the image must lie inside the staged box to use shared memory
       const int wx0 = max(u0 + ilo, 0), wx1 = min(u0 + ihi, w - 1), wy0 = max(v0 - rd, 0), wy1 = min(v0 + rd, h - 1);
       const bool in_box = staged && wx0 >= b.x0 && wx1 < b.x0 + b.bw && wy0 >= b.y0 && wy1 < b.y0 + b.bh;
+#if RT_STATS
+      atomicAdd(&g_rt_stats[d & 7][0], 1ull);
+      if (!in_box) atomicAdd(&g_rt_stats[d & 7][1], 1ull);
+#endif
+#if RT_LINEAR
+      if (wx0 <= wx1 && wy0 <= wy1) {
+        constexpr int NJ = 2 * RADIUS + 1;
+        int uc[NJ], vc[NJ], roff[NJ], coff[NJ], best = -1;
+        unsigned rmask = 0, cmask = 0;
+#pragma unroll
+        for (int k = 0; k < NJ; k++) {
+          const int u = u0 + (k - RADIUS) * d, v = v0 + (k - RADIUS) * d;
+          cmask |= (u >= 0 && u < w) ? 1u << k : 0u;
+          rmask |= (v >= 0 && v < h) ? 1u << k : 0u;
+          uc[k] = min(max(u, 0), w - 1);  // clamped coordinates lie in the clipped window, hence in the box
+          vc[k] = min(max(v, 0), h - 1);
+        }
+        if (in_box) {
+#pragma unroll
+          for (int k = 0; k < NJ; k++) {
+            roff[k] = (vc[k] - b.y0) * b.bw * (FDIM / 8);
+            coff[k] = (uc[k] - b.x0) * (FDIM / 8);
+          }
+          const uint4 *base = reinterpret_cast<const uint4 *>(box_mem);
+          auto load = [&](int off, int ch) { return base[off + ch]; };
+          scan_level<FDIM, RADIUS>(q, roff, coff, rmask, cmask, d == dilation_max, load, max_score, best);
+        } else {
+#pragma unroll
+          for (int k = 0; k < NJ; k++) {
+            roff[k] = vc[k] * w * (FDIM / 8);  // h*w*FDIM/8 < 2^31: checked by the host
+            coff[k] = uc[k] * (FDIM / 8);
+          }
+          const uint4 *base = reinterpret_cast<const uint4 *>(img);
+          auto load = [&](int off, int ch) { return __ldg(base + off + ch); };
+          scan_level<FDIM, RADIUS>(q, roff, coff, rmask, cmask, d == dilation_max, load, max_score, best);
+        }
+        if (best >= 0) {
+          u_new = u0 + (best / NJ - RADIUS) * d;
+          v_new = v0 + (best % NJ - RADIUS) * d;
+        }
+      }
+#else
       if (wx0 <= wx1 && wy0 <= wy1) {
         if (in_box) {
           const uint4 *base = reinterpret_cast<const uint4 *>(box_mem);
@@ -407,6 +554,7 @@ refine_tile_kernel(const __half *__restrict__ D11, const __half *__restrict__ D2
           }
         }
       }
+#endif
     }
     if (split && !pass) continue;  // second half of this level next, same centres
     u0 = u_new;

@@ -45,4 +45,13 @@ out["match_fused_us"] = timeit(lambda i: matching.match(sets[i]["X11"], sets[i][
 # checksum of the refined pixels: identical across builds when the result is bit-identical
 (p,) = be.refine_matches(sets[0]["D11h"], sets[0]["D21h"], sets[0]["p1"], cfg["radius"], cfg["dilation_max"])
 out["checksum"] = int((p.view(-1) * torch.arange(1, p.numel() + 1, device=dev)).sum().item())
+if hasattr(be._lib, "b200slam_internal_refine_stats"):  # -DRT_STATS=1 builds: counters of ONE call on set 0
+    import ctypes
+    buf = (ctypes.c_ulonglong * 32)()
+    be._lib.b200slam_internal_refine_stats(buf)
+    be.refine_matches(sets[0]["D11h"], sets[0]["D21h"], sets[0]["p1"], cfg["radius"], cfg["dilation_max"])
+    torch.cuda.synchronize()
+    be._lib.b200slam_internal_refine_stats(buf)
+    out["stats_by_dilation"] = {d: {"live": buf[4 * d], "out_of_box": buf[4 * d + 1], "tiles_overflow": buf[4 * d + 2],
+                                    "tiles_merged": buf[4 * d + 3]} for d in range(1, 8) if buf[4 * d] or buf[4 * d + 3]}
 print(json.dumps(out))
