@@ -19,6 +19,13 @@
 #include "dev_cache.cuh"
 #include "refine_tile.cuh"
 
+#ifndef RT_QPQ
+#define RT_QPQ 0  // A/B builds: the quarter-warp-per-query-pair kernel (experiments/refine_qpq.cuh, measured slower)
+#endif
+#if RT_QPQ
+#include "../../experiments/refine_qpq.cuh"
+#endif
+
 #ifndef RT_BAND_FIXED
 #define RT_BAND_FIXED 6
 #endif
@@ -208,6 +215,20 @@ extern "C" int b200slam_internal_refine_f16(const void *D11, const void *D21, co
     long long nominal = (long long)(rtile::TW + 2 * reach + rtile::SLACK) * (rtile::TH + 2 * reach + rtile::SLACK) * fdim * 2;
 #if !RT_LINEAR
     if (nominal > rtile::BOX_BYTES) nominal = (long long)(rtile::TW + reach + 2) * (rtile::TH + 2 * reach + 2) * fdim * 2;
+#endif
+#if RT_QPQ
+    if (h < 16000 && w < 16000 &&
+        (long long)rtile::qpq_pitch16(rtile::TW + 2 * reach + rtile::SLACK, 3) * 16 * (rtile::TH + 2 * reach + rtile::SLACK) <=
+            rtile::QPQ_BOX_BYTES) {
+      constexpr int smem = rtile::QPQ_BOX_BYTES + rtile::THREADS / 2 * 24 * 4;
+      static b200dev::Once attr_q;  // function attributes are per device
+      if (attr_q.first())
+        cudaFuncSetAttribute(rtile::refine_qpq_kernel<24, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+      rtile::refine_qpq_kernel<24, 3><<<dim3(tiles, b), rtile::THREADS, smem, st>>>(a, q, p1, p1_new, h, w, n, w, bands,
+                                                                                    dilation_max, lin_out);
+      if (used_tile) *used_tile = 1;
+      return (int)cudaGetLastError();
+    }
 #endif
     if (nominal <= rtile::BOX_BYTES) {
       static b200dev::Once attr;  // function attributes are per device
