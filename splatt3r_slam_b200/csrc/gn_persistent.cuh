@@ -49,6 +49,8 @@ gn_persistent_kernel(float *Twc, const float *__restrict__ Xs, const float *__re
   const int stride = 4 * gper;  // points per smem array
   const int npts = 4 * max(g_end - g_begin, 0);
 
+  const bool stamper = threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0;  // State::prof[0..2]: start, points staged, loop done
+  if (stamper) state->prof[0] = gtimer();
   // ---- prologue: stage this CTA's points ---------------------------------------------------------
   {
     const float *Xi_base = Xs + (size_t)ix * n * 3, *Xj_base = Xs + (size_t)jx * n * 3;
@@ -127,6 +129,7 @@ gn_persistent_kernel(float *Twc, const float *__restrict__ Xs, const float *__re
   __shared__ bool is_last;
   if (tid < 16) pose_sm[tid] = __ldcg(Twc + 8 * (tid < 8 ? ix : jx) + (tid & 7));
   __syncthreads();
+  if (stamper) state->prof[1] = gtimer();
   for (int it = 0; it < max_iter; it++) {
     const EdgePose P = rel_pose(pose_sm, pose_sm + 8);
 
@@ -181,6 +184,7 @@ gn_persistent_kernel(float *Twc, const float *__restrict__ Xs, const float *__re
     __syncthreads();
     if (flag_sm) break;  // ||dx|| < delta: same early exit on every CTA
   }
+  if (stamper) state->prof[2] = gtimer();
 }
 
 }  // namespace b200gn

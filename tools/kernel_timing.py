@@ -65,6 +65,8 @@ for iters in (1, 10):
 ws = be._workspaces[("cuda", 0)]
 st = ws[:48].cpu().view(torch.int64)[2:6].tolist()
 out["gn_tracker_tail_ns"] = {"finalize": st[1] - st[0], "assemble_chol": st[2] - st[1], "finish": st[3] - st[2]}
+pf = ws[88:136].cpu().view(torch.int64).tolist()  # State::prof[0..2] of the persistent kernel: start, points staged, loop done
+out["gn_tracker_kernel_ns"] = {"prologue": pf[1] - pf[0], "iterations": pf[2] - pf[1]}
 # on-device frame tracker (8f rank 2) on a 512x384-point problem; reference restatement on the host beside it
 import time  # noqa: E402
 from oracle import tracker_ref  # noqa: E402
@@ -83,6 +85,9 @@ out["track_ray_dist"]["cpu_threads"] = torch.get_num_threads()
 del sets
 torch.cuda.empty_cache()
 
+if "--no-graph" in sys.argv:
+    print(json.dumps(out))
+    sys.exit(0)
 # ---- graph iteration split ------------------------------------------------------------------
 N, E = 32, 128
 if "--graph" in sys.argv:
