@@ -84,7 +84,10 @@ __device__ __forceinline__ bool iter_proj_core(const float *__restrict__ img, in
 
       const int u2 = (int)floorf(un), v2 = (int)floorf(vn);
       const Weights k2 = bilinear_weights(__fsub_rn(un, (float)u2), __fsub_rn(vn, (float)v2));
-      if (u2 != tu || v2 != tv) {  // another cell: reload (usually an L1 hit: neighbouring lanes sample neighbouring cells)
+#ifndef IP_NO_RELOAD  // -DIP_NO_RELOAD: WRONG results, timing bound only — what a free tap reload (any staging scheme) could gain at most
+#define IP_NO_RELOAD 0
+#endif
+      if (!IP_NO_RELOAD && (u2 != tu || v2 != tv)) {  // another cell: reload (usually an L1 hit: neighbouring lanes sample neighbouring cells)
         load_taps<9>(T, img, hw, w, u2, v2);
         tu = u2;
         tv = v2;
