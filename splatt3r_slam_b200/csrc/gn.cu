@@ -255,22 +255,89 @@ __device__ __forceinline__ int64_t id_at(const int64_t *ii, const int64_t *jj, i
   return p < E ? ii[p] : jj[p - E];
 }
 __global__ void first_occurrence_kernel(const int64_t *__restrict__ ii, const int64_t *__restrict__ jj, int E,
-                                        uint8_t *__restrict__ first) {
+                                        uint8_t *__restrict__ first, const int64_t *gate) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= 2 * E) return;
+  if (p >= 2 * E || (gate && gate[p] >= 0)) return;  // gate: rows already computed by rows_bitmap_kernel
   const int64_t x = id_at(ii, jj, E, p);
   bool f = true;
   for (int q = 0; q < p && f; q++) f = id_at(ii, jj, E, q) != x;
   first[p] = f ? 1 : 0;
 }
 __global__ void rank_kernel(const int64_t *__restrict__ ii, const int64_t *__restrict__ jj, int E,
-                            const uint8_t *__restrict__ first, int64_t *__restrict__ rows) {
+                            const uint8_t *__restrict__ first, int64_t *rows, int gated) {
   const int p = blockIdx.x * blockDim.x + threadIdx.x;
-  if (p >= 2 * E) return;
+  if (p >= 2 * E || (gated && rows[p] >= 0)) return;  // (a thread reads only its own slot before writing it)
   const int64_t x = id_at(ii, jj, E, p);
   int r = 0;
   for (int q = 0; q < 2 * E; q++) r += (first[q] && id_at(ii, jj, E, q) < x) ? 1 : 0;
   rows[p] = r;  // rows[0..E) = ii_row, rows[E..2E) = jj_row
+}
+
+// Large edge lists (2E > 1024): O(E) instead of O(E^2).  ONE CTA: id range by a block reduction; when the range fits
+// the scratch as a presence bitmap (range <= 16 E ids and <= ROWS_BM_WORDS words: keyframe ids are small integers),
+// set the bits, exclusive prefix-popcount over the words in shared memory, row = prefix[word] + popcount(lower bits).
+// Otherwise every rows[p] is set to -1 and the two quadratic kernels above (gated per thread on rows[p] < 0) do the
+// work, so the result never depends on the id values.
+constexpr int ROWS_BM_WORDS = 8192;  // 32 KB of shared memory: id range <= 262 144
+__global__ void __launch_bounds__(1024)
+rows_bitmap_kernel(const int64_t *__restrict__ ii, const int64_t *__restrict__ jj, int E, unsigned *__restrict__ bm,
+                   size_t bm_bytes, int64_t *__restrict__ rows) {
+  __shared__ long long red_lo[32], red_hi[32];
+  __shared__ int pref[ROWS_BM_WORDS];
+  __shared__ int wsum[32];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, n2 = 2 * E;
+  long long lo = 0x7fffffffffffffffll, hi = -0x7fffffffffffffffll - 1;
+  for (int p = tid; p < n2; p += 1024) {
+    const long long x = id_at(ii, jj, E, p);
+    lo = x < lo ? x : lo;
+    hi = x > hi ? x : hi;
+  }
+  for (int o = 16; o > 0; o >>= 1) {
+    const long long a = __shfl_xor_sync(0xffffffffu, lo, o), b = __shfl_xor_sync(0xffffffffu, hi, o);
+    lo = a < lo ? a : lo;
+    hi = b > hi ? b : hi;
+  }
+  if (lane == 0) { red_lo[warp] = lo; red_hi[warp] = hi; }
+  __syncthreads();
+  lo = red_lo[0]; hi = red_hi[0];
+  for (int k = 1; k < 32; k++) { lo = red_lo[k] < lo ? red_lo[k] : lo; hi = red_hi[k] > hi ? red_hi[k] : hi; }
+  const unsigned long long range = (unsigned long long)hi - (unsigned long long)lo + 1ull;  // 0 on full-range wrap
+  const unsigned long long words = (range + 31ull) >> 5;
+  if (range == 0 || words > (unsigned long long)ROWS_BM_WORDS || words * 4ull > bm_bytes) {
+    for (int p = tid; p < n2; p += 1024) rows[p] = -1;  // the quadratic kernels take over
+    return;
+  }
+  const int W = (int)words;
+  for (int k = tid; k < W; k += 1024) bm[k] = 0u;
+  __syncthreads();
+  for (int p = tid; p < n2; p += 1024) {
+    const unsigned long long d = (unsigned long long)id_at(ii, jj, E, p) - (unsigned long long)lo;
+    atomicOr(bm + (d >> 5), 1u << (d & 31ull));
+  }
+  __syncthreads();
+  // exclusive prefix of the word popcounts: thread t owns words [t*C, (t+1)*C)
+  const int C = (W + 1023) / 1024;
+  int local = 0;
+  for (int k = tid * C; k < min(W, (tid + 1) * C); k++) local += __popc(__ldcg(bm + k));
+  int incl = local;
+  for (int o = 1; o < 32; o <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, o);
+    if (lane >= o) incl += v;
+  }
+  if (lane == 31) wsum[warp] = incl;
+  __syncthreads();
+  int base = incl - local;
+  for (int k = 0; k < warp; k++) base += wsum[k];
+  for (int k = tid * C; k < min(W, (tid + 1) * C); k++) {
+    pref[k] = base;
+    base += __popc(__ldcg(bm + k));
+  }
+  __syncthreads();
+  for (int p = tid; p < n2; p += 1024) {
+    const unsigned long long d = (unsigned long long)id_at(ii, jj, E, p) - (unsigned long long)lo;
+    const unsigned w = __ldcg(bm + (d >> 5)), bit = (unsigned)(d & 31ull);
+    rows[p] = pref[d >> 5] + __popc(w & ((1u << bit) - 1u));
+  }
 }
 
 // ---- stage 2 (large problems): one warp per edge -----------------------------------------------

@@ -318,3 +318,26 @@ def test_config3_calib_32_keyframes_128_edges_full_size(backend, ref_backend):
         Tr = G["Twc"].clone()
         run(ref_backend, "calib", Tr, Gd, h, w, 10, 0.0)
         assert rel(Tb, Tr) < RTOL
+
+
+@pytest.mark.parametrize("E,kind", [(8192, "compact"), (8192, "offset_negative"), (700, "compact"), (8192, "huge_range"),
+                                    (8192, "over_bitmap"), (300, "compact")])
+def test_edge_rows_large_lists(backend, E, kind):
+    """Keyframe ids -> rows (torch::_unique + searchsorted, gn_kernels.cu:160-169) on long edge lists: the O(E)
+    presence-bitmap kernel (id range fits the scratch), its quadratic fallback (range too wide) and the short-list
+    path give the rank among the sorted distinct ids, whatever the id values."""
+    g = torch.Generator().manual_seed(E + len(kind))
+    if kind == "compact":
+        ids = torch.randint(0, 1024, (2 * E,), generator=g)
+    elif kind == "offset_negative":
+        ids = torch.randint(0, 3000, (2 * E,), generator=g) * 3 - 4000
+    elif kind == "huge_range":
+        ids = torch.randint(-2**62, 2**62, (2 * E,), generator=g)
+        ids[::7] = ids[0]  # duplicates
+    else:  # range just beyond what the 2E-byte scratch holds as a bitmap (16 E ids)
+        ids = torch.randint(0, 16 * E + 5000, (2 * E,), generator=g)
+        ids[0], ids[1] = 0, 16 * E + 4999
+    ii, jj = ids[:E].contiguous(), ids[E:].contiguous()
+    a, b = backend.edge_rows(ii.to(dev()), jj.to(dev()))
+    uniq = torch.unique(ids)
+    assert torch.equal(torch.cat([a, b]).cpu(), torch.searchsorted(uniq, ids))
