@@ -127,6 +127,12 @@ typedef struct {
   float C_thresh, Q_thresh;
   int height, width, pixel_border; /* calib only */
   float z_eps;                     /* calib only */
+  /* Optional (NULL = identity): device array (N) i64, row k of the solve reads its pointmap / confidence from row
+   * kf_slots[k] of Xs / Cs.  Lets a caller hand the kernels its keyframe BUFFERS (reference frame.py:266-268
+   * SharedKeyframes.X / .C, indexed by keyframe id) in place for ANY set of keyframe ids, where the reference
+   * stacks fresh (N,n,3) / (N,n,1) tensors before every solve (global_opt.py:111-119).  Twc stays the compact
+   * (N,8) array (32 bytes per keyframe). */
+  const int64_t *kf_slots;
 } b200slam_gn_params;
 
 /* Bytes of device workspace the GN entry points need for N poses, E directed edges, n points. */

@@ -161,8 +161,9 @@ build_kernel(float *Twc, const float *__restrict__ Xs, const float *__restrict__
   const int ix = (int)ii_row[e], jx = (int)jj_row[e];
   const EdgePose P = rel_pose(Twc + 8 * ix, Twc + 8 * jx);
 
-  const float *Xi_base = Xs + (size_t)ix * n * 3, *Xj_base = Xs + (size_t)jx * n * 3;
-  const float *Ci_base = Cs + (size_t)ix * n, *Cj_base = Cs + (size_t)jx * n;
+  const size_t xi_slot = C.slots ? (size_t)C.slots[ix] : (size_t)ix, xj_slot = C.slots ? (size_t)C.slots[jx] : (size_t)jx;
+  const float *Xi_base = Xs + xi_slot * n * 3, *Xj_base = Xs + xj_slot * n * 3;
+  const float *Ci_base = Cs + xi_slot * n, *Cj_base = Cs + xj_slot * n;
   const bool second = e >= C.E1;
   const int64_t *idx_e = (second ? C.idx2 : idx) + (size_t)e * n;
   const uint8_t *val_e = (second ? C.valid2 : valid) + (size_t)e * n;

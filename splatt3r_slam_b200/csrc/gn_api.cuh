@@ -17,6 +17,7 @@ inline BuildConsts make_consts(const b200slam_gn_params *p, const float *K) {
   C.vlo = (float)p->pixel_border;
   C.vhi = (float)(p->height - 1 - p->pixel_border);
   C.width = p->width > 0 ? p->width : 1;
+  C.slots = p->kf_slots;
   return C;
 }
 

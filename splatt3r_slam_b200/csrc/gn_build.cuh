@@ -103,6 +103,8 @@ struct BuildConsts {
   // 16-byte loads are legal: n % 4 == 0 AND every base pointer is 16-byte aligned (valid: 4-byte); a
   // contiguous view with an odd storage offset takes the scalar path instead of faulting
   int vec_ok = 0;
+  // optional rank -> buffer slot map for Xs / Cs (b200slam_gn_params::kf_slots); nullptr = identity
+  const int64_t *slots = nullptr;
 };
 
 // One point.  Xi/ci = matched point of keyframe i, Xj/cj = point k of keyframe j.

@@ -4,9 +4,10 @@ solve_GN_rays, solve_GN_calib) on plain tensors — and the device-resident vari
 asks for:
 
   * the reference stacks the pointmaps / confidences / poses of all N keyframes into fresh tensors for
-    every solve (3.1 MB per keyframe at 512x384) — `keyframe_views` returns zero-copy views of the shared
-    keyframe buffers when the graph's keyframe ids are 0..N-1 (the normal case: every keyframe has an edge
-    to its predecessor) and gathers only otherwise;
+    every solve (3.1 MB per keyframe at 512x384) — here the kernels read the shared keyframe buffers IN PLACE for
+    any set of keyframe ids: views when the ids are 0..N-1 (the normal case: every keyframe has an edge to its
+    predecessor), otherwise the whole buffers plus the id list as the backend's `kf_slots` map (row k of the
+    solve reads buffer row ids[k]); only the N x 8 pose rows are gathered and scattered back (32 bytes each);
   * the reference concatenates every per-edge array with its reverse (2.56 MB per edge) — the backend's
     two-way entry reads the one-way lists in place.
 
@@ -32,13 +33,15 @@ def prep_two_way_edges(graph):
 
 
 def keyframe_views(X_buf, C_buf, T_buf, unique_kf_idx):
-    """(Xs, Cs, poses, zero_copy): rows `unique_kf_idx` of the buffers — views when the ids are 0..N-1."""
+    """(Xs, Cs, poses, kf_slots): the pointmaps / confidences of keyframes `unique_kf_idx` WITHOUT copying them.
+    ids 0..N-1: views of the first N buffer rows, poses updated in place, kf_slots None.  Any other id set: the whole
+    buffers with kf_slots = the ids (the backend reads row ids[k] for node k) and a gathered (N,8) pose array that the
+    caller scatters back."""
     N = unique_kf_idx.numel()
     contiguous_ids = bool((unique_kf_idx[0] == 0) & (unique_kf_idx[-1] == N - 1))  # sorted + distinct => 0..N-1
     if contiguous_ids:
-        return X_buf[:N], C_buf[:N], T_buf[:N], True
-    return (X_buf.index_select(0, unique_kf_idx), C_buf.index_select(0, unique_kf_idx),
-            T_buf.index_select(0, unique_kf_idx), False)
+        return X_buf[:N], C_buf[:N], T_buf[:N], None
+    return X_buf, C_buf, T_buf.index_select(0, unique_kf_idx), unique_kf_idx.contiguous()
 
 
 def _solve(kind_args, graph, X_buf, C_buf, T_buf, K, cfg, backend):
@@ -49,12 +52,12 @@ def _solve(kind_args, graph, X_buf, C_buf, T_buf, K, cfg, backend):
     unique_kf_idx = get_unique_kf_idx(graph)
     if unique_kf_idx.numel() <= pin:
         return None
-    Xs, Cs, poses, zero_copy = keyframe_views(X_buf, C_buf, T_buf, unique_kf_idx)
-    prm = backend.make_params(*kind_args(cfg))
+    Xs, Cs, poses, kf_slots = keyframe_views(X_buf, C_buf, T_buf, unique_kf_idx)
+    prm = backend.make_params(*kind_args(cfg), kf_slots=kf_slots)
     (dx,) = backend.gauss_newton_twoway(prm, poses, Xs, Cs, K, graph.ii, graph.jj, graph.idx_ii2jj, graph.idx_jj2ii,
                                         graph.valid_match_j, graph.valid_match_i, graph.Q_ii2jj, graph.Q_jj2ii,
                                         cfg["max_iters"], cfg["delta_norm"])
-    if not zero_copy:  # update_T_WCs(T_WCs[pin:], unique_kf_idx[pin:])
+    if kf_slots is not None:  # update_T_WCs(T_WCs[pin:], unique_kf_idx[pin:])
         T_buf.index_copy_(0, unique_kf_idx[pin:], poses[pin:])
     return dx
 

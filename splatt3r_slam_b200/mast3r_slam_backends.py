@@ -22,7 +22,8 @@ GN_RAYS, GN_CALIB, GN_POINTS = 0, 1, 2
 class GNParams(ctypes.Structure):
     _fields_ = [("kind", ctypes.c_int), ("sigma_a", ctypes.c_float), ("sigma_b", ctypes.c_float),
                 ("C_thresh", ctypes.c_float), ("Q_thresh", ctypes.c_float), ("height", ctypes.c_int),
-                ("width", ctypes.c_int), ("pixel_border", ctypes.c_int), ("z_eps", ctypes.c_float)]
+                ("width", ctypes.c_int), ("pixel_border", ctypes.c_int), ("z_eps", ctypes.c_float),
+                ("kf_slots", ctypes.c_void_p)]  # optional device (N) i64: row k reads Xs / Cs row kf_slots[k]
 
 
 def _load():
@@ -386,7 +387,7 @@ def gauss_newton_twoway(prm, Twc, Xs, Cs, K, ii, jj, idx_ii2jj, idx_jj2ii, valid
             valid_match_i=valid_match_i, Q_ii2jj=Q_ii2jj, Q_jj2ii=Q_jj2ii)
     if K is not None:
         _contig(K=K)
-    N, n, E1 = Xs.shape[0], Xs.shape[1], ii.shape[0]
+    N, n, E1 = Twc.shape[0], Xs.shape[1], ii.shape[0]  # (with prm.kf_slots, Xs / Cs are whole keyframe buffers)
     ptrs = (_cuda(Twc, torch.float32, "Twc"), _cuda(Xs, torch.float32, "Xs"), _cuda(Cs, torch.float32, "Cs"),
             (_cuda(K, torch.float32, "K") if K is not None else None), _cuda(ii, torch.int64, "ii"),
             _cuda(jj, torch.int64, "jj"), _cuda(idx_ii2jj, torch.int64, "idx_ii2jj"),
@@ -406,8 +407,16 @@ def gauss_newton_twoway(prm, Twc, Xs, Cs, K, ii, jj, idx_ii2jj, idx_jj2ii, valid
 
 
 # ---- extras beyond the reference module (used by tests, bench and the multi-GPU driver) ----------
-def make_params(kind, sigma_a, sigma_b, C_thresh, Q_thresh, height=0, width=0, pixel_border=0, z_eps=0.0):
-    return GNParams(kind, sigma_a, sigma_b, C_thresh, Q_thresh, int(height), int(width), int(pixel_border), z_eps)
+def make_params(kind, sigma_a, sigma_b, C_thresh, Q_thresh, height=0, width=0, pixel_border=0, z_eps=0.0, kf_slots=None):
+    """`kf_slots` (optional (N,) int64 CUDA tensor): row k of the solve reads its pointmap / confidence from row
+    kf_slots[k] of Xs / Cs (keyframe buffers used in place); the tensor must outlive the calls made with the params."""
+    prm = GNParams(kind, sigma_a, sigma_b, C_thresh, Q_thresh, int(height), int(width), int(pixel_border), z_eps, None)
+    if kf_slots is not None:
+        if not (kf_slots.is_cuda and kf_slots.dtype == torch.int64 and kf_slots.is_contiguous()):
+            raise RuntimeError("kf_slots must be a contiguous int64 CUDA tensor")
+        prm.kf_slots = kf_slots.data_ptr()
+        prm._keep = kf_slots
+    return prm
 
 
 def gn_build_blocks(prm, Twc, Xs, Cs, K, ii, jj, idx, valid, Q):

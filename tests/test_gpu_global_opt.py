@@ -44,7 +44,9 @@ def test_twoway_equals_concatenated(backend, N, Eu, h, w):
     assert not torch.equal(T_ref[1:], G["Twc"][1:])
 
 
-def test_non_contiguous_keyframe_ids_gather_and_scatter(backend):
+def test_non_contiguous_keyframe_ids_read_the_buffers_in_place(backend):
+    """Any id set: the pointmap / confidence buffers go to the kernels as they are (kf_slots map), only the pose rows
+    are gathered and scattered; poses bit-identical to the reference's stack + cat sequence."""
     N, Eu, h, w = 5, 6, 24, 32
     G, graph = one_way_graph(N, Eu, h, w, seed=4)
     ids = torch.tensor([1, 4, 5, 8, 9], device=DEV)  # keyframe ids of the 5 graph nodes in a 12-slot buffer
@@ -58,6 +60,8 @@ def test_non_contiguous_keyframe_ids_gather_and_scatter(backend):
     C_buf = torch.rand((12,) + tuple(G["Cs"].shape[1:]), device=DEV); C_buf[ids] = G["Cs"]
     T_buf = torch.zeros((12, 8), device=DEV); T_buf[:, 6:] = 1.0; T_buf[ids] = G["Twc"]
     untouched = T_buf.clone()
+    Xv, Cv, _, slots = global_opt.keyframe_views(X_buf, C_buf, T_buf, ids)
+    assert Xv.data_ptr() == X_buf.data_ptr() and Cv.data_ptr() == C_buf.data_ptr() and torch.equal(slots, ids)
     global_opt.solve_GN_rays(graph, X_buf, C_buf, T_buf, cfg=cfg)
     assert torch.equal(T_buf[ids], T_ref)
     mask = torch.ones(12, dtype=torch.bool, device=DEV); mask[ids] = False
@@ -76,3 +80,25 @@ def test_calib_twoway(backend):
     T_buf = G["Twc"].clone()
     global_opt.solve_GN_calib(graph, G["Xs"], G["Cs"], T_buf, G["K"], (h, w), cfg=cfg)
     assert torch.equal(T_buf, T_ref)
+
+
+@pytest.mark.parametrize("N,Eu,h,w,name", [(2, 1, 96, 128, "rays"), (12, 60, 24, 32, "calib"), (40, 60, 24, 32, "rays")])
+def test_kf_slots_on_every_gn_path(backend, N, Eu, h, w, name):
+    """The slot map through the persistent kernel (N = 2), the fused per-iteration path and the large-graph path."""
+    G, graph = one_way_graph(N, Eu, h, w, seed=3 * N + Eu)
+    ids = (torch.arange(N, device=DEV) * 2 + 3)  # keyframe ids 3, 5, 7, ... in a (2N + 4)-slot buffer
+    cap = 2 * N + 4
+    gslots = SimpleNamespace(**vars(graph))
+    gslots.ii, gslots.jj = ids[graph.ii].contiguous(), ids[graph.jj].contiguous()
+    cfg = dict(global_opt.DEFAULT_CFG, max_iters=3, delta_norm=0.0)
+    X_buf = torch.randn((cap,) + tuple(G["Xs"].shape[1:]), device=DEV); X_buf[ids] = G["Xs"]
+    C_buf = torch.rand((cap,) + tuple(G["Cs"].shape[1:]), device=DEV); C_buf[ids] = G["Cs"]
+    T_buf = torch.zeros((cap, 8), device=DEV); T_buf[:, 6:] = 1.0; T_buf[ids] = G["Twc"]
+    T_ref = G["Twc"].clone()
+    if name == "rays":
+        global_opt.solve_GN_rays(graph, G["Xs"], G["Cs"], T_ref, cfg=cfg)
+        global_opt.solve_GN_rays(gslots, X_buf, C_buf, T_buf, cfg=cfg)
+    else:
+        global_opt.solve_GN_calib(graph, G["Xs"], G["Cs"], T_ref, G["K"], (h, w), cfg=cfg)
+        global_opt.solve_GN_calib(gslots, X_buf, C_buf, T_buf, G["K"], (h, w), cfg=cfg)
+    assert torch.equal(T_buf[ids], T_ref) and not torch.equal(T_ref[1:], G["Twc"][1:])
