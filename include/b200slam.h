@@ -257,6 +257,29 @@ int b200slam_gauss_newton_twoway(const b200slam_gn_params *prm, float *Twc, cons
                                  int max_iter, float delta_thresh, float *dx, void *workspace,
                                  size_t workspace_bytes, void *stream);
 
+/* Forward 3D-Gaussian-splat tile rasteriser (last item).  Replaces the FORWARD pass of
+ * the reference's vendored rasteriser, thirdparty/diff-gaussian-rasterization-modified: RasterizeGaussiansCUDA
+ * (rasterize_points.cu:39-130) -> CudaRasterizer::Rasterizer::forward (cuda_rasterizer/rasterizer_impl.cu:195-330:
+ * preprocessCUDA forward.cu:157-260, duplicateWithKeys / sort / identifyTileRanges, renderCUDA forward.cu:262-370),
+ * as the SLAM system calls it for rendering (splatt3r_slam/visualization.py:563-596,
+ * splatt3r_core/src/pixelsplat_src/cuda_splatting.py:96-124).  The backward pass is not provided.
+ * All pointers are device pointers unless noted.  means3D (P,3); cov3D_precomp (P,6) upper triangle, or NULL with
+ * scales (P,3) + rotations (P,4) quaternion (r,x,y,z); opacities (P); colors_precomp (P,3), or NULL with shs
+ * (P,sh_coeffs,3) of degree sh_degree <= 3 and campos (3); viewmatrix / projmatrix (16) in the reference's layout
+ * (the transposed 4x4 matrices GaussianRasterizationSettings carries); bg (3) -> out_color (3,H,W) f32, radii (P) i32.
+ * The number of (splat, tile) instances is data dependent: the workspace is sized for max_instances
+ * (b200slam_gs_workspace_bytes); the call reads the actual count on the host (one stream synchronisation, as the
+ * reference does at rasterizer_impl.cu:289), stores it in *num_instances (host pointer, may be NULL) and returns
+ * B200SLAM_EWORKSPACE without rendering when it exceeds max_instances — call again with a larger workspace. */
+size_t b200slam_gs_workspace_bytes(int P, int H, int W, long long max_instances);
+int b200slam_gs_render(const float *means3D, const float *cov3D_precomp, const float *scales,
+                       const float *rotations, float scale_modifier, const float *opacities,
+                       const float *colors_precomp, const float *shs, int sh_degree, int sh_coeffs,
+                       const float *campos, const float *viewmatrix, const float *projmatrix, float tan_fovx,
+                       float tan_fovy, const float *bg, int P, int H, int W, float *out_color, int *radii,
+                       long long max_instances, long long *num_instances, void *workspace,
+                       size_t workspace_bytes, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -272,3 +272,59 @@ def make_track_problem_calib(seed=0, h=48, w=64, noise=0.001, invalid=0.2, devic
     d = {k: t.to(device) for k, t in d.items()}
     d["img_size"] = (h, w)
     return d
+
+
+def make_splat_scene(seed=0, P=2000, H=96, W=128, fov_deg=60.0, sh_coeffs=16, identity_camera=False):
+    """A synthetic 3D-Gaussian scene + camera in the conventions of the reference's rasteriser calls
+    (splatt3r_core/src/pixelsplat_src/cuda_splatting.py:77-124): `viewmatrix` = transposed world->camera matrix,
+    `projmatrix` = viewmatrix @ transposed perspective matrix, `campos` = camera centre; splats in front of, behind and
+    beside the camera, a few very large and very small ones.  `identity_camera`: camera frame == world frame, so the view
+    depth of a splat is its z coordinate EXACTLY in every implementation, and a tenth of the splats are given the depth of
+    another one (order ties, resolved by splat index).  (With a rotated camera, near-equal depths would be ordered by the
+    last bit of a 3-term fp32 sum — a property of the rounding, not of the algorithm.)
+    Returns CPU float32 tensors: means (P,3), cov (P,6), scales (P,3), rotations (P,4) [r,x,y,z; cov == cov3D(scales,
+    rotations)], opacities (P,1), colors (P,3), shs (P,sh_coeffs,3), view (4,4), proj (4,4), campos (3), bg (3), and the
+    floats tanfovx, tanfovy."""
+    g = torch.Generator().manual_seed(seed)
+    r = lambda *s: torch.rand(*s, generator=g, dtype=torch.float64)
+    rn = lambda *s: torch.randn(*s, generator=g, dtype=torch.float64)
+    tanx = math.tan(math.radians(fov_deg) / 2)
+    tany = tanx * H / W
+    # camera-to-world: small random rotation + translation
+    ax = rn(3); ax = ax / ax.norm(); ang = 0.3
+    Kx = torch.tensor([[0, -ax[2], ax[1]], [ax[2], 0, -ax[0]], [-ax[1], ax[0], 0]], dtype=torch.float64)
+    R = torch.eye(3, dtype=torch.float64) + math.sin(ang) * Kx + (1 - math.cos(ang)) * (Kx @ Kx)
+    c2w = torch.eye(4, dtype=torch.float64); c2w[:3, :3] = R; c2w[:3, 3] = rn(3) * 0.5
+    if identity_camera:
+        R = torch.eye(3, dtype=torch.float64)
+        c2w = torch.eye(4, dtype=torch.float64)
+    # points in the camera frame
+    z = 0.6 + 5.0 * r(P)
+    z[: P // 20] = -1.0 - r(P // 20)                    # behind the camera
+    z[P // 20: P // 10] = 0.05 + 0.2 * r(P // 10 - P // 20)   # around the 0.2 near cull
+    x = (2.6 * r(P) - 1.3) * tanx * z.abs()             # up to 1.3x outside the frustum
+    y = (2.6 * r(P) - 1.3) * tany * z.abs()
+    pc = torch.stack([x, y, z], 1)
+    if identity_camera:
+        pc = pc.float().double()
+        pc[P // 2: P // 2 + P // 10, 2] = pc[P // 2 - P // 10: P // 2, 2]  # exactly equal view depths
+    means = (pc @ R.T + c2w[:3, 3]).float()
+    scales = (0.01 + 0.06 * r(P, 3)) * z.abs()[:, None] * 0.5
+    scales[-8:] *= 12.0                                 # a few huge splats (hundreds of tiles)
+    scales[-16:-8] *= 0.01                              # and tiny ones (low-pass filter dominates)
+    q = rn(P, 4); q = q / q.norm(dim=1, keepdim=True)
+    rr, xx, yy, zz = q[:, 0], q[:, 1], q[:, 2], q[:, 3]
+    Rq = torch.stack([torch.stack([1 - 2 * (yy * yy + zz * zz), 2 * (xx * yy - rr * zz), 2 * (xx * zz + rr * yy)], 1),
+                      torch.stack([2 * (xx * yy + rr * zz), 1 - 2 * (xx * xx + zz * zz), 2 * (yy * zz - rr * xx)], 1),
+                      torch.stack([2 * (xx * zz - rr * yy), 2 * (yy * zz + rr * xx), 1 - 2 * (xx * xx + yy * yy)], 1)], 1)
+    Sigma = Rq @ torch.diag_embed(scales ** 2) @ Rq.transpose(1, 2)
+    cov = torch.stack([Sigma[:, 0, 0], Sigma[:, 0, 1], Sigma[:, 0, 2], Sigma[:, 1, 1], Sigma[:, 1, 2], Sigma[:, 2, 2]], 1).float()
+    near, far = 0.1, 100.0
+    Pj = torch.zeros(4, 4, dtype=torch.float64)
+    Pj[0, 0], Pj[1, 1], Pj[3, 2] = 1 / tanx, 1 / tany, 1.0
+    Pj[2, 2], Pj[2, 3] = far / (far - near), -(far * near) / (far - near)
+    view = torch.linalg.inv(c2w).T.contiguous()
+    proj = (view @ Pj.T).contiguous()
+    return dict(means=means, cov=cov, scales=scales.float(), rotations=q.float(), opacities=(0.05 + 0.95 * r(P, 1)).float(),
+                colors=r(P, 3).float(), shs=(rn(P, sh_coeffs, 3) * 0.3).float(), view=view.float(), proj=proj.float(),
+                campos=c2w[:3, 3].float(), bg=torch.tensor([0.1, 0.2, 0.3]), tanfovx=tanx, tanfovy=tany, H=H, W=W)

@@ -5,5 +5,5 @@ set -e
 NAME=$1; shift
 cd "$(dirname "$0")/../splatt3r_slam_b200/csrc"
 nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -Xcompiler -fPIC -Xptxas -v -I. "$@" -c refine.cu -o /tmp/refine_ab_$NAME.o 2>&1 | grep -A2 "refine_tile" | grep -E "spill|Used"
-nvcc -shared -o ../libb200slam_ab_$NAME.so matching.o /tmp/refine_ab_$NAME.o gn.o 2>/dev/null
+nvcc -shared -o ../libb200slam_ab_$NAME.so matching.o /tmp/refine_ab_$NAME.o gn.o gs_raster.o 2>/dev/null
 ls -la ../libb200slam_ab_$NAME.so
