@@ -127,3 +127,47 @@ def ref_cuda_block(cfg, sets, reps=10):
             "matched_px_per_s": N_PIX / (step_ms * 1e-3),
             "what": "reference CUDA extension (oracle/_ref: /root/reference sources, 4 host-line edits for torch 2.11, "
                     "device code untouched) timed per call on the same rotating inputs"}
+
+
+def gs_render_block(reps=10, keyframes=4, H=384, W=512):
+    """SURVEY.md 8f rank 4 (last item): the forward 3DGS rasteriser on a scene of the shape the SLAM viewer renders — one
+    Gaussian per pixel of `keyframes` 512x384 keyframes (visualization.py:470-596: all accumulated Gaussians, precomputed
+    covariances and colours) — through the mirror of the reference's GaussianRasterizer, and the reference's own CUDA
+    build (oracle/_ref/diffgauss_ref.so, when it travelled) on the same tensors."""
+    import torch
+    from splatt3r_slam_b200 import synthetic
+    from splatt3r_slam_b200.gaussian_rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+    dev = torch.device("cuda", torch.cuda.current_device())
+    P = keyframes * H * W
+    S = synthetic.make_splat_scene(seed=9, P=P, H=H, W=W)
+    S["scales"] = S["scales"] * 0.08   # pixel-sized splats, as one Gaussian per pointmap pixel gives
+    S["cov"] = S["cov"] * 0.08 ** 2
+    d = {k: (v.to(dev) if torch.is_tensor(v) else v) for k, v in S.items()}
+    rs = GaussianRasterizationSettings(H, W, S["tanfovx"], S["tanfovy"], d["bg"], 1.0, d["view"], d["proj"], 0, d["campos"],
+                                       False, False)
+    R = GaussianRasterizer(rs)
+    mg = torch.zeros_like(d["means"])
+    ours = lambda i: R(d["means"], mg, d["opacities"], colors_precomp=d["colors"], cov3D_precomp=d["cov"])
+    color, radii = ours(0)
+    t_ours = _time_us(ours, reps, 1)
+    vis = int((radii > 0).sum())
+    out = {"workload": f"{P} splats ({keyframes} keyframes x {H}x{W}), {H}x{W} image, precomputed covariance + colour",
+           "visible_splats": vis, "us": t_ours, "splats_per_s": P / (t_ours * 1e-6),
+           # bytes the forward pass has to touch at least once: inputs (3+6+1+3 floats per splat) + image
+           "algorithmic_GBps": (P * 13 * 4 + 3 * H * W * 4) / (t_ours * 1e-6) / 1e9}
+    so = os.path.join(ROOT, "oracle", "_ref", "diffgauss_ref.so")
+    if os.path.exists(so):
+        try:
+            spec = importlib.util.spec_from_file_location("diffgauss_ref", so)
+            ref = importlib.util.module_from_spec(spec)
+            spec.loader.exec_module(ref)
+            e = torch.empty(0, device=dev)
+            fn = lambda i: ref.rasterize_gaussians(d["bg"], d["means"], d["colors"], d["opacities"], e, e, 1.0, d["cov"], d["view"],
+                                                   d["proj"], S["tanfovx"], S["tanfovy"], H, W, e, 0, d["campos"], False, False)
+            rc = fn(0)[1]
+            out["ref_cuda_us"] = _time_us(fn, reps, 1)
+            out["max_abs_diff_vs_ref"] = float((rc - color).abs().max())
+        except Exception as exc:  # noqa: BLE001
+            out["ref_cuda_us"] = None
+            out["ref_error"] = str(exc)[:200]
+    return out

@@ -56,7 +56,7 @@ def cpu_baseline_tracker():
 def run_tracker(args):
     rank, world, local = _init_dist(args)
     dev = torch.device("cuda", local)
-    from bench_extra import batched_matching_block, bind_numa, ref_cuda_block
+    from bench_extra import batched_matching_block, bind_numa, gs_render_block, ref_cuda_block
     numa = bind_numa(local)  # before any pinned allocation: the rank's arena lands on its GPU's node
     from splatt3r_slam_b200 import matching
     import splatt3r_slam_b200.mast3r_slam_backends as be
@@ -201,6 +201,12 @@ def run_tracker(args):
     if world == 1:
         batched = batched_matching_block(be, cfg, sets)
         ref_cuda = ref_cuda_block(cfg, sets)
+    gs = None
+    if world == 1 and not args.no_graph:
+        try:
+            gs = gs_render_block()
+        except Exception as exc:  # noqa: BLE001  (a side block must not take the headline down)
+            gs = {"error": str(exc)[:200]}
     peak, peak_src = peaks()
     dom = max(kt, key=lambda k: kt[k])
     alg = {"iter_proj": B_ITER_PROJ * N_PIX, "refine": B_REFINE * N_PIX,
@@ -243,6 +249,7 @@ def run_tracker(args):
         "graph_cfg3": graph_cfg3,        # configs[2]: gauss_newton_calib, 32 keyframes / 128 edges, 1 GPU
         "match_batched": batched,        # iter_proj / refine at b = 8 and 32 pairs per call
         "ref_cuda": ref_cuda,            # the reference's CUDA build on the same box and inputs
+        "gs_render": gs,                 # forward 3DGS rasteriser, ours and the reference build
     }
     if not args.no_cpu_baseline and world == 1:
         line["cpu_baseline"] = cpu_baseline_tracker()
