@@ -21,7 +21,7 @@ _lib.b200slam_gs_render.argtypes = ([_vp] * 4 + [_f] + [_vp] * 3 + [_i, _i] + [_
                                     ctypes.c_longlong, ctypes.POINTER(ctypes.c_longlong), _vp, ctypes.c_size_t, _vp])
 _lib.b200slam_gs_render.restype = _i
 EWORKSPACE = -2
-_workspaces = {}  # device index -> (uint8 tensor, instance capacity it was sized for)
+_workspaces = {}  # (device index, stream) -> (uint8 tensor, instance capacity): calls on different streams must not share it
 
 
 class GaussianRasterizationSettings(NamedTuple):
@@ -61,14 +61,15 @@ def rasterize_gaussians(means3D, means2D, sh, colors_precomp, opacities, scales,
         color = torch.empty((3, H, W), dtype=torch.float32, device=dev)
         radii = torch.zeros((P,), dtype=torch.int32, device=dev)
         stream = torch.cuda.current_stream(dev).cuda_stream
-        ws, cap = _workspaces.get(dev.index, (None, 0))
+        key = (dev.index, stream)
+        ws, cap = _workspaces.get(key, (None, 0))
         need = ctypes.c_longlong(0)
         cap = max(cap, 8 * P + 1024)
         for _ in range(3):
             nbytes = _lib.b200slam_gs_workspace_bytes(P, H, W, cap)
             if ws is None or ws.numel() < nbytes:
                 ws = torch.empty(nbytes, dtype=torch.uint8, device=dev)
-            _workspaces[dev.index] = (ws, cap)
+            _workspaces[key] = (ws, cap)
             rc = _lib.b200slam_gs_render(ptr(t["means"]), ptr(t["cov"]), ptr(t["sc"]), ptr(t["rot"]), float(rs.scale_modifier),
                                          ptr(t["op"]), ptr(t["col"]), ptr(t["sh"]), int(rs.sh_degree), sh_coeffs, ptr(t["cam"]),
                                          ptr(t["view"]), ptr(t["proj"]), float(rs.tanfovx), float(rs.tanfovy), ptr(t["bg"]), P, H,
