@@ -439,6 +439,19 @@ __device__ inline void finalize_small(const float *Twc, const int64_t *ii_row, c
                                       double *out, double (*sc)[FIN_SCRATCH], double *tmp) {
   const int tid = threadIdx.x, items = E * NACC;
   const int NC = NT / items > 0 ? NT / items : 1;
+  // The pose row this thread's M entry needs (below) is requested BEFORE the partial sums: its two dependent L2 round
+  // trips (edge row, then pose) overlap the partials' round trip instead of following it.
+  float Tpre[8];
+  if (tid < E * 49) {
+    const float *Tp = Twc + 8 * (int)ii_row[tid / 49];
+    if ((reinterpret_cast<uintptr_t>(Tp) & 15) == 0) {  // rows of a (N,8) tensor are 32-byte aligned unless it is an offset view
+      const float4 lo = reinterpret_cast<const float4 *>(Tp)[0], hi = reinterpret_cast<const float4 *>(Tp)[1];
+      Tpre[0] = lo.x; Tpre[1] = lo.y; Tpre[2] = lo.z; Tpre[3] = lo.w; Tpre[4] = hi.x; Tpre[5] = hi.y; Tpre[6] = hi.z; Tpre[7] = hi.w;
+    } else {
+#pragma unroll
+      for (int k = 0; k < 8; k++) Tpre[k] = Tp[k];
+    }
+  }
   for (int t = tid; t < items * NC; t += NT) {
     const int item = t % items, chunk = t / items, e = item / NACC, l = item - e * NACC;
     const double *p = partials + (size_t)e * S * NACC + l;
@@ -457,7 +470,7 @@ __device__ inline void finalize_small(const float *Twc, const int64_t *ii_row, c
   }
   for (int t = tid; t < E * 49; t += NT) {
     const int e = t / 49, o = t - e * 49;
-    sc[e][36 + o] = adj_inv_entry(Twc + 8 * (int)ii_row[e], o / 7, o % 7);
+    sc[e][36 + o] = t == tid ? adj_inv_entry(Tpre, o / 7, o % 7) : adj_inv_entry(Twc + 8 * (int)ii_row[e], o / 7, o % 7);
   }
   __syncthreads();
   for (int t = tid; t < items; t += NT) {
@@ -511,7 +524,7 @@ __device__ inline bool solve7(const double *Hu, const double *g, double *x) {
 #pragma unroll
     for (int k = 0; k < j; k++) d -= L[j][k] * L[j][k];
     ok = ok && (d > 0.0);
-    const double dinv = 1.0 / sqrt(d);
+    const double dinv = rsqrt(d);  // one MUFU + Newton steps instead of a square root AND a division per column (as gn_chol_blocked.cuh)
     L[j][j] = dinv;  // reciprocal diagonal
 #pragma unroll
     for (int i = j + 1; i < 7; i++) {
