@@ -44,3 +44,21 @@ def test_oracle_invariants():
     S0 = dict(S); S0["opacities"] = S["opacities"] * 0
     c0, _ = run(S0, True, False)
     assert np.allclose(c0, S["bg"].numpy()[:, None, None])
+
+
+def test_rasterizer_mirror_argument_checks_without_a_gpu():
+    """The mirror of the reference's GaussianRasterizer raises the reference's own exceptions for bad argument
+    combinations (diff_gaussian_rasterization/__init__.py:190-194) and refuses CPU tensors (no CPU path)."""
+    import torch
+    from splatt3r_slam_b200.gaussian_rasterizer import GaussianRasterizationSettings, GaussianRasterizer
+    S = synthetic.make_splat_scene(seed=1, P=16, H=16, W=16)
+    rs = GaussianRasterizationSettings(16, 16, S["tanfovx"], S["tanfovy"], S["bg"], 1.0, S["view"], S["proj"], 0, S["campos"],
+                                       False, False)
+    R = GaussianRasterizer(rs)
+    with pytest.raises(Exception, match="excatly one of either SHs"):
+        R(S["means"], None, S["opacities"], shs=S["shs"], colors_precomp=S["colors"], cov3D_precomp=S["cov"])
+    with pytest.raises(Exception, match="exactly one of either scale/rotation"):
+        R(S["means"], None, S["opacities"], colors_precomp=S["colors"])
+    with pytest.raises(RuntimeError, match="no CPU path"):
+        R(S["means"], None, S["opacities"], colors_precomp=S["colors"], cov3D_precomp=S["cov"])
+    assert torch.is_tensor(S["cov"]) and S["cov"].shape == (16, 6)
