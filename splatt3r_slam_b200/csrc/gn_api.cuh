@@ -423,11 +423,12 @@ extern "C" int b200slam_gn_status(const void *workspace, int *iters, int *done, 
 
 // Block products up to which the single-CTA block-sparse factorisation beats what runs otherwise when conjugate
 // gradients do not converge on a ring-like graph, the dense tiled Cholesky.  Measured on B200 (tools/sparse_probe.py,
-// profiles/r02c_sparse_probe.txt): sparse 0.39 us per block product (0.26 ms at 368 products ... 19.6 ms at 49 584),
+// profiles/r02c_sparse_probe.txt): sparse 0.25-0.3 us per block product once the updates of a block are accumulated
+// in registers (0.25 ms at 368 products, 1.41 ms at 3 531, 2.85 ms at 9 561; 0.39 us before),
 // dense 0.93 / 2.09 / 3.7 / 11.7 ms at N = 130 / 300 / 512 / 1024 = 5.8e-3 N + 5.3e-9 N^3 ms.
 inline long long sparse_work_limit(int N, long long layout_cap) {
   const double dense_ms = 5.8e-3 * N + 5.3e-9 * (double)N * N * N;
-  const long long by_cost = (long long)(dense_ms / 0.39e-3);
+  const long long by_cost = (long long)(dense_ms / 0.30e-3);
   return by_cost < layout_cap ? by_cost : layout_cap;
 }
 

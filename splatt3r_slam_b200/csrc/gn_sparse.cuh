@@ -119,25 +119,50 @@ sparse_solve_retract_kernel(float *Twc, const double *__restrict__ eb, int N, Sp
         const int j = P.level_cols[c];
         double *D = P.Dg + (size_t)j * 49;
         const int sbase = P.colptr[j];
-        for (int t = P.upd_ptr[j]; t < P.upd_ptr[j + 1]; t++) {
-          const int ds = P.upd[3 * t + 2];
-          if (g > 1 && ((ds < 0 ? 0 : 1 + ds - sbase) % g) != sub) continue;  // warp-uniform
-          const double *A = P.Lv + (size_t)P.upd[3 * t] * 49, *Bk = P.Lv + (size_t)P.upd[3 * t + 1] * 49;
-          double *dst = ds < 0 ? D : P.Lv + (size_t)ds * 49;
-          blkA[warp][lane] = A[lane];
-          blkB[warp][lane] = Bk[lane];
-          if (lane + 32 < 49) { blkA[warp][lane + 32] = A[lane + 32]; blkB[warp][lane + 32] = Bk[lane + 32]; }
-          __syncwarp();
-          double s0 = 0.0, s1 = 0.0;
-#pragma unroll
-          for (int q = 0; q < 7; q++) {
-            s0 = fma(blkA[warp][r0 * 7 + q], blkB[warp][c0 * 7 + q], s0);
-            if (lane + 32 < 49) s1 = fma(blkA[warp][r1 * 7 + q], blkB[warp][c1 * 7 + q], s1);
+        // The triples of a column are grouped by destination block (plan): the warp reads their indices 32 at a time
+        // (one coalesced round trip instead of one per triple), accumulates the products of one destination in
+        // registers and subtracts them from the block ONCE (the first version paid three dependent L2 round trips per
+        // triple: indices, source blocks, read-modify-write of the destination).
+        const int t_end = P.upd_ptr[j + 1];
+        double acc0 = 0.0, acc1 = 0.0;
+        int cur_ds = -2;  // -2: nothing accumulated yet (-1 is the diagonal block)
+        bool cur_mine = false;
+        auto flush = [&]() {
+          if (cur_ds != -2 && cur_mine) {
+            double *dst = cur_ds < 0 ? D : P.Lv + (size_t)cur_ds * 49;
+            dst[lane] -= acc0;
+            if (lane + 32 < 49) dst[lane + 32] -= acc1;
           }
-          dst[lane] -= s0;
-          if (lane + 32 < 49) dst[lane + 32] -= s1;
-          __syncwarp();
+        };
+        for (int tb = P.upd_ptr[j]; tb < t_end; tb += 32) {
+          const int tt = tb + lane;
+          int ia = 0, ib = 0, ids = -2;
+          if (tt < t_end) { ia = P.upd[3 * tt]; ib = P.upd[3 * tt + 1]; ids = P.upd[3 * tt + 2]; }
+          const int cnt = min(32, t_end - tb);
+          for (int q = 0; q < cnt; q++) {
+            const int ds = __shfl_sync(0xffffffffu, ids, q);
+            if (ds != cur_ds) {  // warp-uniform
+              flush();
+              cur_ds = ds;
+              cur_mine = g == 1 || ((ds < 0 ? 0 : 1 + ds - sbase) % g) == sub;
+              acc0 = acc1 = 0.0;
+            }
+            if (!cur_mine) continue;
+            const double *A = P.Lv + (size_t)__shfl_sync(0xffffffffu, ia, q) * 49;
+            const double *Bk = P.Lv + (size_t)__shfl_sync(0xffffffffu, ib, q) * 49;
+            blkA[warp][lane] = A[lane];
+            blkB[warp][lane] = Bk[lane];
+            if (lane + 32 < 49) { blkA[warp][lane + 32] = A[lane + 32]; blkB[warp][lane + 32] = Bk[lane + 32]; }
+            __syncwarp();
+#pragma unroll
+            for (int qq = 0; qq < 7; qq++) {
+              acc0 = fma(blkA[warp][r0 * 7 + qq], blkB[warp][c0 * 7 + qq], acc0);
+              if (lane + 32 < 49) acc1 = fma(blkA[warp][r1 * 7 + qq], blkB[warp][c1 * 7 + qq], acc1);
+            }
+            __syncwarp();
+          }
         }
+        flush();
       }
     }
     __syncthreads();

@@ -19,6 +19,7 @@
 #include <math.h>
 
 #include <algorithm>
+#include <array>
 #include <cmath>
 #include <vector>
 
@@ -165,15 +166,18 @@ inline bool analyze(const int64_t *ii_row, const int64_t *jj_row, int E, int N, 
   std::vector<int> where(M, -1);  // position -> slot within the destination column
   for (int j = 0; j < M; j++) {
     for (int s = P.colptr[j]; s < P.colptr[j + 1]; s++) where[P.rowidx[s]] = s;
+    std::vector<std::array<int, 3>> trip;
     for (size_t t = 0; t < rows[j].size(); t += 2) {
       const int k = rows[j][t], sb = rows[j][t + 1];  // L_jk lives in slot sb of column k
       for (int sa = sb; sa < P.colptr[k + 1]; sa++) {  // rows i >= j of column k (ascending: sb is row j itself)
         const int i = P.rowidx[sa];
-        P.upd.push_back(sa);
-        P.upd.push_back(sb);
-        P.upd.push_back(i == j ? -1 : where[i]);
+        trip.push_back({sa, sb, i == j ? -1 : where[i]});
       }
     }
+    // grouped by DESTINATION block (stable: the sources of one block keep their column order), so that the numeric
+    // kernel accumulates all updates of a block in registers and touches the block once
+    std::stable_sort(trip.begin(), trip.end(), [](const std::array<int, 3> &a, const std::array<int, 3> &b) { return a[2] < b[2]; });
+    for (const auto &tr : trip) { P.upd.push_back(tr[0]); P.upd.push_back(tr[1]); P.upd.push_back(tr[2]); }
     P.upd_ptr[j + 1] = (int)P.upd.size() / 3;
     for (int s = P.colptr[j]; s < P.colptr[j + 1]; s++) where[P.rowidx[s]] = -1;
   }
