@@ -19,6 +19,8 @@
 //     conservative culling aids; the render kernel stages it per batch with 16-byte loads, lets every warp pick the
 //     splats that can reach its 8 x 4 pixel block with one ballot per 32 splats, and skips expf below the cut-off.
 #include <cub/cub.cuh>
+#include <thrust/iterator/counting_iterator.h>
+#include <thrust/iterator/transform_iterator.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -172,22 +174,22 @@ gs_preprocess_kernel(int P, const float *__restrict__ means, const float *__rest
   s2[idx] = make_float4(cb, ex, ey, sane ? thr : -3.0e38f);
 }
 
-// tiles touched, in depth order (input of the exclusive scan)
-__global__ void gs_gather_counts_kernel(int P, const uint32_t *__restrict__ ids_sorted, const uint32_t *__restrict__ tiles_touched,
-                                        uint32_t *__restrict__ counts_sorted) {
-  const int s = blockIdx.x * blockDim.x + threadIdx.x;
-  if (s < P) counts_sorted[s] = tiles_touched[ids_sorted[s]];
-}
+// tiles touched by the splat at depth rank s: the scan reads it through this functor (no gathered copy)
+struct CountInDepthOrder {
+  const uint32_t *ids_sorted, *tiles_touched;
+  __host__ __device__ __forceinline__ uint32_t operator()(int s) const { return tiles_touched[ids_sorted[s]]; }
+};
+using CountIter = thrust::transform_iterator<CountInDepthOrder, thrust::counting_iterator<int>>;
 
 // instances in depth order: key = tile, value = splat (rasterizer_impl.cu:78-120 emits (tile | depth) keys instead)
-__global__ void gs_emit_kernel(int P, const uint32_t *__restrict__ ids_sorted, const uint32_t *__restrict__ offsets,
+__global__ void gs_emit_kernel(int P, const uint32_t *__restrict__ ids_sorted, const uint32_t *__restrict__ incl,
                                const ushort4 *__restrict__ rects, int tiles_x, long long capacity,
                                uint32_t *__restrict__ keys, uint32_t *__restrict__ vals) {
   const int s = blockIdx.x * blockDim.x + threadIdx.x;
   if (s >= P) return;
   const uint32_t g = ids_sorted[s];
   const ushort4 r = rects[g];
-  long long off = offsets[s];
+  long long off = (long long)incl[s] - (long long)((r.z - r.x) * (r.w - r.y));  // inclusive sum minus this splat's own tiles
   for (int y = r.y; y < r.w; y++)
     for (int x = r.x; x < r.z; x++) {
       if (off < capacity) {
@@ -305,7 +307,7 @@ inline GsLayout gs_layout(int P, int H, int W, long long cap) {
   size_t t1 = 0, t2 = 0, t3 = 0;
   cub::DoubleBuffer<uint32_t> dk(nullptr, nullptr), dv(nullptr, nullptr);
   cub::DeviceRadixSort::SortPairs(nullptr, t1, dk, dv, (int)p, 0, 32);
-  cub::DeviceScan::ExclusiveSum(nullptr, t2, (uint32_t *)nullptr, (uint32_t *)nullptr, (int)p);
+  cub::DeviceScan::InclusiveSum(nullptr, t2, CountIter(thrust::counting_iterator<int>(0), CountInDepthOrder{nullptr, nullptr}), (uint32_t *)nullptr, (int)p);
   cub::DeviceRadixSort::SortPairs(nullptr, t3, dk, dv, (int)(c < 0x7fffffffull ? c : 0x7fffffffull), 0, tile_bits(tiles));
   L.temp_bytes = t1 > t2 ? (t1 > t3 ? t1 : t3) : (t2 > t3 ? t2 : t3);
   L.temp = take(L.temp_bytes);
@@ -360,18 +362,18 @@ extern "C" int b200slam_gs_render(const float *means3D, const float *cov3D_preco
     size_t tb = L.temp_bytes;
     err = cub::DeviceRadixSort::SortPairs(ws + L.temp, tb, dk, dv, P, 0, 32, st);  // splats by view depth (stable)
     if (err != cudaSuccess) return (int)err;
-    gs_gather_counts_kernel<<<pb, 256, 0, st>>>(P, dv.Current(), touched, counts);
     tb = L.temp_bytes;
-    err = cub::DeviceScan::ExclusiveSum(ws + L.temp, tb, counts, offsets, P, st);
+    err = cub::DeviceScan::InclusiveSum(ws + L.temp, tb, CountIter(thrust::counting_iterator<int>(0), CountInDepthOrder{dv.Current(), touched}),
+                                        offsets, P, st);
     if (err != cudaSuccess) return (int)err;
     // the instance count decides the launch sizes below: one host read per call, like the reference
     // (rasterizer_impl.cu:289)
-    uint32_t last[2] = {0, 0};
-    err = cudaMemcpyAsync(&last[0], offsets + (P - 1), 4, cudaMemcpyDeviceToHost, st);
-    if (err == cudaSuccess) err = cudaMemcpyAsync(&last[1], counts + (P - 1), 4, cudaMemcpyDeviceToHost, st);
+    uint32_t last = 0;
+    err = cudaMemcpyAsync(&last, offsets + (P - 1), 4, cudaMemcpyDeviceToHost, st);
     if (err == cudaSuccess) err = cudaStreamSynchronize(st);
     if (err != cudaSuccess) return (int)err;
-    total = (long long)last[0] + last[1];
+    total = (long long)last;
+    (void)counts;
     if (num_instances) *num_instances = total;
     if (total > max_instances || total > 0x7fffffffll) return B200SLAM_EWORKSPACE;  // retry with a larger workspace
     if (total > 0) {

@@ -44,6 +44,9 @@ def _f32(t, name):
         return None
     if not t.is_cuda:
         raise RuntimeError(f"{name} must be a CUDA tensor (this rasteriser has no CPU path)")
+    if t.dtype == torch.float32 and t.is_contiguous():
+        return t  # (no new tensor object: eleven arguments per call, each conversion costs microseconds of host time
+        #          during which the GPU idles - the call synchronises once in the middle)
     return t.detach().to(torch.float32).contiguous()
 
 
