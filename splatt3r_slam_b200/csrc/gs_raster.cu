@@ -160,7 +160,8 @@ gs_preprocess_kernel(int P, const float *__restrict__ means, const float *__rest
   // power = -0.5 (A dx^2 + C dy^2) - B dx dy = a dx^2 + c dy^2 + b dx dy with the conic pre-scaled (exact: powers of two)
   const float op = opacities[idx];
   s0[idx] = make_float4(ix, iy, -0.5f * conA, -conB);
-  s1[idx] = make_float4(-0.5f * conC, op, cr, cg);
+  // s1 = {conic c, cut-off exponent, opacity, red}, s2 = {green, blue, extent x, extent y}: a pixel that rejects the
+  // splat reads s0 and s1 only
   // Culling aids for the render kernel, CONSERVATIVE by construction (they only skip work whose result is known):
   // a pixel takes a term iff alpha = min(0.99, op * exp(power)) >= 1/255, i.e. power >= -log(255 op).  thr sits 1e-3
   // below that (far more than the rounding of expf and of the product), and (ex, ey) is the half-extent of the
@@ -171,7 +172,8 @@ gs_preprocess_kernel(int P, const float *__restrict__ means, const float *__rest
   const bool sane = op == op && det > 0.0f && cxx > 0.0f && cyy > 0.0f;
   const float ex = !sane ? 3.0e38f : never ? -1.0f : sqrtf(-2.0f * thr * cxx) + 0.5f;
   const float ey = !sane ? 3.0e38f : never ? -1.0f : sqrtf(-2.0f * thr * cyy) + 0.5f;
-  s2[idx] = make_float4(cb, ex, ey, sane ? thr : -3.0e38f);
+  s1[idx] = make_float4(-0.5f * conC, sane ? thr : -3.0e38f, op, cr);
+  s2[idx] = make_float4(cg, cb, ex, ey);
 }
 
 // tiles touched by the splat at depth rank s: the scan reads it through this functor (no gathered copy)
@@ -252,7 +254,7 @@ gs_render_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ 
         const int j = j0 + lane;
         const float4 a = c0[j < nb ? j : 0], e = c2[j < nb ? j : 0];
         const float ddx = a.x - fminf(fmaxf(a.x, fx0), fx1), ddy = a.y - fminf(fmaxf(a.y, fy0), fy1);
-        mask = __ballot_sync(0xffffffffu, j < nb && fabsf(ddx) <= e.y && fabsf(ddy) <= e.z);
+        mask = __ballot_sync(0xffffffffu, j < nb && fabsf(ddx) <= e.z && fabsf(ddy) <= e.w);
       }
       while (mask) {
         const int j = j0 + __ffs(mask) - 1;
@@ -260,16 +262,16 @@ gs_render_kernel(const uint2 *__restrict__ ranges, const uint32_t *__restrict__ 
         if (done) continue;
         const float4 a = c0[j];
         const float4 b = c1[j];
-        const float4 e = c2[j];
         const float dx = a.x - pixx, dy = a.y - pixy;
         const float power = a.z * dx * dx + b.x * dy * dy + a.w * dx * dy;
-        if (power > 0.0f || power < e.w) continue;  // e.w: surely below the 1/255 cut-off (the exact test follows)
-        const float alpha = fminf(0.99f, b.y * expf(power));
+        if (power > 0.0f || power < b.y) continue;  // b.y: surely below the 1/255 cut-off (the exact test follows)
+        const float alpha = fminf(0.99f, b.z * expf(power));
         if (alpha < 1.0f / 255.0f) continue;
         const float test_T = T * (1.0f - alpha);
         if (test_T < 0.0001f) { done = true; continue; }
+        const float4 e = c2[j];
         const float wgt = alpha * T;
-        Cr += b.z * wgt; Cg += b.w * wgt; Cb += e.x * wgt;
+        Cr += b.w * wgt; Cg += e.x * wgt; Cb += e.y * wgt;
         T = test_T;
       }
       if (__all_sync(0xffffffffu, done)) break;
