@@ -270,7 +270,8 @@ int b200slam_gauss_newton_twoway(const b200slam_gn_params *prm, float *Twc, cons
  * The number of (splat, tile) instances is data dependent: the workspace is sized for max_instances
  * (b200slam_gs_workspace_bytes); the call reads the actual count on the host (one stream synchronisation, as the
  * reference does at rasterizer_impl.cu:289), stores it in *num_instances (host pointer, may be NULL) and returns
- * B200SLAM_EWORKSPACE without rendering when it exceeds max_instances — call again with a larger workspace. */
+ * B200SLAM_EWORKSPACE without rendering when it exceeds max_instances — call again with a larger workspace.
+ * Limits: H, W <= 65535 * 16; fewer than 2^31 instances per call (a scene beyond that must be rendered in parts). */
 size_t b200slam_gs_workspace_bytes(int P, int H, int W, long long max_instances);
 int b200slam_gs_render(const float *means3D, const float *cov3D_precomp, const float *scales,
                        const float *rotations, float scale_modifier, const float *opacities,
