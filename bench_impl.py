@@ -224,9 +224,9 @@ def run_tracker(args):
                 "api": "matching.match(X11, X21, D11, D21, fused=True) [f32 pointmaps + f16 descriptors from host] + "
                        "mast3r_slam_backends.gauss_newton_rays",
                 "numa": numa},
-        # per step: repack_planar + iter_proj + refine_tile + first_occurrence + rank + ONE persistent GN kernel
-        # (all 10 iterations; cooperative launch) = 6 launches of this library's kernels
-        "gpu_launches": args.steps * 6,
+        # per step: repack_planar + iter_proj + refine_tile + rows_small + ONE persistent GN kernel
+        # (all 10 iterations; cooperative launch) = 5 launches of this library's kernels
+        "gpu_launches": args.steps * 5,
         "kernel_us": {k: round(v, 2) for k, v in kt.items()},
         "match_px_per_s": N_PIX / ((kt["iter_proj"] + kt["refine"]) * 1e-6),
         "gn_iters_per_s": {"E2": GN["iters"] / (kt["gn"] * 1e-6)},

@@ -274,6 +274,30 @@ __global__ void rank_kernel(const int64_t *__restrict__ ii, const int64_t *__res
   rows[p] = r;  // rows[0..E) = ii_row, rows[E..2E) = jj_row
 }
 
+// Short edge lists (2E <= 1024, every tracker / local-window call): both quadratic phases in ONE single-CTA launch
+// (shared-memory copy of the ids, block barrier between the phases) instead of two launches.
+__global__ void __launch_bounds__(1024)
+rows_small_kernel(const int64_t *__restrict__ ii, const int64_t *__restrict__ jj, int E, int64_t *__restrict__ rows) {
+  __shared__ long long ids[1024];
+  __shared__ unsigned char first[1024];
+  const int p = threadIdx.x, n2 = 2 * E;
+  if (p < n2) ids[p] = id_at(ii, jj, E, p);
+  __syncthreads();
+  if (p < n2) {
+    const long long x = ids[p];
+    bool f = true;
+    for (int q = 0; q < p && f; q++) f = ids[q] != x;
+    first[p] = f ? 1 : 0;
+  }
+  __syncthreads();
+  if (p < n2) {
+    const long long x = ids[p];
+    int r = 0;
+    for (int q = 0; q < n2; q++) r += (first[q] && ids[q] < x) ? 1 : 0;
+    rows[p] = r;
+  }
+}
+
 // Large edge lists (2E > 1024): O(E) instead of O(E^2).  ONE CTA: id range by a block reduction; when the range fits
 // the scratch as a presence bitmap (range <= 16 E ids and <= ROWS_BM_WORDS words: keyframe ids are small integers),
 // set the bits, exclusive prefix-popcount over the words in shared memory, row = prefix[word] + popcount(lower bits).

@@ -632,7 +632,11 @@ extern "C" int b200slam_edge_rows(const int64_t *ii, const int64_t *jj, int E, i
   // the quadratic kernels cost 2.7e8 comparisons at E = 8192 (0.1 ms) and nothing at tracker sizes: large lists go
   // through the O(E) bitmap kernel first, which leaves rows[p] = -1 for the quadratic ones only when the id range
   // does not fit the scratch
-  const bool big = 2 * E > 1024 && ((uintptr_t)scratch % 4 == 0);
+  if (2 * E <= 1024) {
+    rows_small_kernel<<<1, 1024, 0, st>>>(ii, jj, E, rows);
+    return (int)cudaGetLastError();
+  }
+  const bool big = ((uintptr_t)scratch % 4 == 0);
   if (big) rows_bitmap_kernel<<<1, 1024, 0, st>>>(ii, jj, E, (unsigned *)scratch, scratch_bytes, rows);
   first_occurrence_kernel<<<blocks, 128, 0, st>>>(ii, jj, E, (uint8_t *)scratch, big ? rows : nullptr);
   rank_kernel<<<blocks, 128, 0, st>>>(ii, jj, E, (const uint8_t *)scratch, rows, big ? 1 : 0);
